@@ -1,0 +1,105 @@
+// capi_linear.cu — C ABI for the QKV / o_proj dense layers (include/ffb200.h).
+// Mirrors Kernels::Linear::forward_kernel_wrapper / inference_kernel_wrapper
+// (src/ops/kernels/linear_kernels.cu:133-140,187-195): out = in * W^T (+ bias).
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+#include "common.cuh"
+
+namespace ffb {
+int launch_linear_stream(int dtype, int quant, void const *in, void *out, void const *w, void const *bias, int M,
+                         int K, int N, cudaStream_t s);
+// tcgen05/TMA GEMM for batched prompt/tree tokens (linear_tc.cu)
+int linear_tc_supported(int dtype, int quant, int K, int N);
+int launch_linear_tc(struct LinearTcState *st, int dtype, int quant, void const *in, void *out, void const *w,
+                     void const *bias, int M, int K, int N, cudaStream_t s);
+struct LinearTcState *linear_tc_create(int dtype, int quant, int K, int N, int max_batch);
+void linear_tc_destroy(struct LinearTcState *st);
+} // namespace ffb
+
+struct ffb_linear_s {
+  ffb_linear_desc d;
+  ffb::LinearTcState *tc = nullptr;
+};
+
+using namespace ffb;
+
+extern "C" {
+
+int ffb_linear_create(ffb_linear_desc const *desc, ffb_linear_t *out) {
+  FFB_REQUIRE(desc && out, "null argument");
+  ffb_linear_desc const &d = *desc;
+  FFB_REQUIRE(d.dtype == FFB_DT_HALF || d.dtype == FFB_DT_BF16, "dtype %d not supported (half/bf16 only)", d.dtype);
+  FFB_REQUIRE(d.quant_type == FFB_DT_NONE || d.quant_type == FFB_DT_INT8 || d.quant_type == FFB_DT_INT4,
+              "quant_type %d not supported", d.quant_type);
+  FFB_REQUIRE(d.in_dim > 0 && d.out_dim > 0 && d.in_dim % 128 == 0 && d.out_dim % 32 == 0,
+              "linear needs in_dim %% 128 == 0 and out_dim %% 32 == 0 (got %d -> %d)", d.in_dim, d.out_dim);
+  FFB_REQUIRE(d.max_batch > 0 && d.max_batch <= FFB_MAX_NUM_TOKENS, "max_batch %d out of range", d.max_batch);
+  if (d.activation != 0) {
+    set_error("activation %d: only AC_MODE_NONE is on the attention hot path", d.activation);
+    return FFB_ERR_UNSUPPORTED;
+  }
+  int rc = ffb_check_device();
+  if (rc != FFB_OK) {
+    return rc;
+  }
+  ffb_linear_s *h = new (std::nothrow) ffb_linear_s();
+  FFB_REQUIRE(h, "out of host memory");
+  h->d = d;
+  if (linear_tc_supported(d.dtype, d.quant_type, d.in_dim, d.out_dim)) {
+    h->tc = linear_tc_create(d.dtype, d.quant_type, d.in_dim, d.out_dim, d.max_batch);
+    if (!h->tc) {
+      delete h;
+      return FFB_ERR_CUDA;
+    }
+  }
+  *out = h;
+  return FFB_OK;
+}
+
+int ffb_linear_destroy(ffb_linear_t h) {
+  if (h) {
+    if (h->tc) {
+      linear_tc_destroy(h->tc);
+    }
+    delete h;
+  }
+  return FFB_OK;
+}
+
+int ffb_linear_forward(ffb_linear_t h, void const *in, void *out, void const *w, void const *bias, int batch,
+                       ffb_stream_t stream) {
+  FFB_REQUIRE(h && in && out && w, "null argument");
+  FFB_REQUIRE(batch >= 0 && batch <= h->d.max_batch, "batch %d exceeds max_batch %d", batch, h->d.max_batch);
+  if (batch == 0) {
+    return FFB_OK;
+  }
+  ffb_linear_desc const &d = h->d;
+  cudaStream_t s = (cudaStream_t)stream;
+  // FFB_LINEAR=stream|tc forces a path (tests / profiling)
+  char const *force = getenv("FFB_LINEAR");
+  int const tc_min = 65; // below this the GEMM is a weight stream (AI = M flop/B << ridge ~ 250)
+  bool use_tc = h->tc && batch >= tc_min;
+  if (force && strcmp(force, "stream") == 0) {
+    use_tc = false;
+  } else if (force && strcmp(force, "tc") == 0) {
+    FFB_REQUIRE(h->tc, "FFB_LINEAR=tc but the tcgen05 path does not support this shape");
+    use_tc = true;
+  }
+  if (use_tc) {
+    return launch_linear_tc(h->tc, d.dtype, d.quant_type, in, out, w, bias, batch, d.in_dim, d.out_dim, s);
+  }
+  size_t const elt = 2;
+  for (int m0 = 0; m0 < batch; m0 += 64) {
+    int const m = batch - m0 < 64 ? batch - m0 : 64;
+    int rc = launch_linear_stream(d.dtype, d.quant_type, (char const *)in + (size_t)m0 * d.in_dim * elt,
+                                  (char *)out + (size_t)m0 * d.out_dim * elt, w, bias, m, d.in_dim, d.out_dim, s);
+    if (rc != FFB_OK) {
+      return rc;
+    }
+  }
+  return FFB_OK;
+}
+
+} // extern "C"

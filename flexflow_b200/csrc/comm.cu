@@ -1,0 +1,151 @@
+// comm.cu — head-sharded AllReduce parallel op over NCCL (NVLink 5 / NVSwitch).
+// Replaces Kernels::AllReduce::inference_kernel_wrapper (src/parallel_ops/kernels/allreduce_kernels.cu:56-78)
+// and the communicator bring-up of src/runtime/model.cc:584-628.  NCCL is resolved at run time with
+// dlopen so the library loads (and every other entry point works) in a process without NCCL, and so
+// that inside a PyTorch process the already-loaded libnccl.so.2 is shared instead of duplicated.
+#include <dlfcn.h>
+#include <cstring>
+
+#include <new>
+
+#include "common.cuh"
+
+namespace {
+
+typedef struct ncclComm *ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+enum { ncclSuccess = 0 };
+enum { ncclFloat16 = 6, ncclFloat32 = 7, ncclBfloat16 = 9 }; // nccl.h ncclDataType_t
+enum { ncclSum = 0 };
+
+struct NcclApi {
+  void *lib = nullptr;
+  int (*GetUniqueId)(ncclUniqueId *) = nullptr;
+  int (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+  int (*CommDestroy)(ncclComm_t) = nullptr;
+  int (*AllReduce)(void const *, void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+  char const *(*GetErrorString)(int) = nullptr;
+};
+
+NcclApi *nccl() {
+  static NcclApi api;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    char const *names[] = {"libnccl.so.2", "libnccl.so"};
+    for (char const *n : names) {
+      api.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+      if (api.lib) {
+        break;
+      }
+    }
+    if (api.lib) {
+      api.GetUniqueId = (decltype(api.GetUniqueId))dlsym(api.lib, "ncclGetUniqueId");
+      api.CommInitRank = (decltype(api.CommInitRank))dlsym(api.lib, "ncclCommInitRank");
+      api.CommDestroy = (decltype(api.CommDestroy))dlsym(api.lib, "ncclCommDestroy");
+      api.AllReduce = (decltype(api.AllReduce))dlsym(api.lib, "ncclAllReduce");
+      api.GetErrorString = (decltype(api.GetErrorString))dlsym(api.lib, "ncclGetErrorString");
+    }
+  }
+  if (!api.lib || !api.GetUniqueId || !api.CommInitRank || !api.CommDestroy || !api.AllReduce) {
+    ffb::set_error("NCCL (libnccl.so.2) could not be loaded: %s", dlerror());
+    return nullptr;
+  }
+  return &api;
+}
+
+#define FFB_NCCL_TRY(api, expr)                                                               \
+  do {                                                                                        \
+    int _r = (expr);                                                                          \
+    if (_r != ncclSuccess) {                                                                  \
+      ffb::set_error("%s failed: %s", #expr, (api)->GetErrorString ? (api)->GetErrorString(_r) : "?"); \
+      return FFB_ERR_NCCL;                                                                    \
+    }                                                                                         \
+  } while (0)
+
+} // namespace
+
+struct ffb_comm_s {
+  ncclComm_t comm = nullptr;
+  int nranks = 1, rank = 0;
+  bool owned = false;
+};
+
+extern "C" {
+
+int ffb_comm_get_unique_id(void *id_out) {
+  FFB_REQUIRE(id_out, "null argument");
+  NcclApi *api = nccl();
+  if (!api) {
+    return FFB_ERR_NCCL;
+  }
+  FFB_NCCL_TRY(api, api->GetUniqueId((ncclUniqueId *)id_out));
+  return FFB_OK;
+}
+
+int ffb_comm_init_rank(void const *id, int nranks, int rank, ffb_comm_t *out) {
+  FFB_REQUIRE(id && out && nranks >= 1 && rank >= 0 && rank < nranks, "bad communicator arguments");
+  NcclApi *api = nccl();
+  if (!api) {
+    return FFB_ERR_NCCL;
+  }
+  ffb_comm_s *c = new (std::nothrow) ffb_comm_s();
+  FFB_REQUIRE(c, "out of host memory");
+  c->nranks = nranks;
+  c->rank = rank;
+  c->owned = true;
+  ncclUniqueId uid;
+  memcpy(&uid, id, sizeof(uid));
+  int r = api->CommInitRank(&c->comm, nranks, uid, rank);
+  if (r != ncclSuccess) {
+    ffb::set_error("ncclCommInitRank failed: %s", api->GetErrorString ? api->GetErrorString(r) : "?");
+    delete c;
+    return FFB_ERR_NCCL;
+  }
+  *out = c;
+  return FFB_OK;
+}
+
+int ffb_comm_from_nccl(void *nccl_comm, int nranks, int rank, ffb_comm_t *out) {
+  FFB_REQUIRE(nccl_comm && out, "null argument");
+  ffb_comm_s *c = new (std::nothrow) ffb_comm_s();
+  FFB_REQUIRE(c, "out of host memory");
+  c->comm = (ncclComm_t)nccl_comm;
+  c->nranks = nranks;
+  c->rank = rank;
+  c->owned = false;
+  *out = c;
+  return FFB_OK;
+}
+
+int ffb_comm_destroy(ffb_comm_t c) {
+  if (!c) {
+    return FFB_OK;
+  }
+  if (c->owned && c->comm) {
+    NcclApi *api = nccl();
+    if (api) {
+      api->CommDestroy(c->comm);
+    }
+  }
+  delete c;
+  return FFB_OK;
+}
+
+int ffb_allreduce(ffb_comm_t c, void const *in, void *out, size_t count, int dtype, ffb_stream_t stream) {
+  FFB_REQUIRE(c && in && out, "null argument");
+  if (count == 0) {
+    return FFB_OK;
+  }
+  int const nt = dtype == FFB_DT_HALF ? ncclFloat16 : (dtype == FFB_DT_BF16 ? ncclBfloat16 : (dtype == FFB_DT_FLOAT ? ncclFloat32 : -1));
+  FFB_REQUIRE(nt >= 0, "dtype %d not supported by allreduce", dtype);
+  NcclApi *api = nccl();
+  if (!api) {
+    return FFB_ERR_NCCL;
+  }
+  // same call as allreduce_kernels.cu:67-73
+  FFB_NCCL_TRY(api, api->AllReduce(in, out, count, nt, ncclSum, c->comm, (cudaStream_t)stream));
+  return FFB_OK;
+}
+
+} // extern "C"

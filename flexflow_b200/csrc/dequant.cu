@@ -1,0 +1,98 @@
+// dequant.cu — standalone int4/int8 weight decompression (kept for the bit-exact parity test and for
+// callers that want the dense matrix; the hot path dequantises inside the GEMM, linear_stream.cu).
+// Replaces decompress_int4_general_weights / decompress_int8_general_weights
+// (src/ops/kernels/decompress_kernels.cu:27-70): one thread per ELEMENT there, with two scalar 2-byte
+// meta loads and a half division each.  Here a thread owns 8 consecutive columns of one group (32 rows):
+// scale/offset are fetched once as 128-bit loads, the reciprocal is taken once per column, and 32 rows
+// are emitted as 128-bit stores.
+#include "dequant.cuh"
+
+namespace ffb {
+
+template <typename T, int BITS>
+__global__ void __launch_bounds__(256)
+dequant_kernel(uint8_t const *__restrict__ blob, T *__restrict__ out, int in_dim, int out_dim) {
+  size_t const value_size = (size_t)in_dim * out_dim;
+  size_t const nvalue_bytes = BITS == 4 ? value_size / 2 : value_size;
+  T const *offs = reinterpret_cast<T const *>(blob + nvalue_bytes);
+  T const *scales = offs + value_size / 32;
+  int const cols8 = in_dim / 8;
+  size_t const total = (size_t)(out_dim / 32) * cols8;
+  for (size_t w = blockIdx.x * (size_t)blockDim.x + threadIdx.x; w < total; w += (size_t)gridDim.x * blockDim.x) {
+    int const g = (int)(w / cols8), c8 = (int)(w % cols8);
+    size_t const gi = (size_t)g * in_dim + c8 * 8;
+    uint4 const us = *reinterpret_cast<uint4 const *>(scales + gi);
+    uint4 const uo = *reinterpret_cast<uint4 const *>(offs + gi);
+    T const *ps = reinterpret_cast<T const *>(&us);
+    T const *po = reinterpret_cast<T const *>(&uo);
+    typename DqCoef<T>::type coef[8];
+#pragma unroll
+    for (int e = 0; e < 8; e++) {
+      coef[e] = dq_coef(ps[e], po[e]);
+    }
+    for (int r = 0; r < 32; r++) {
+      size_t const idx = (size_t)(g * 32 + r) * in_dim + c8 * 8;
+      int q[8];
+      if (BITS == 4) {
+        uint32_t const v = *reinterpret_cast<uint32_t const *>(blob + idx / 2);
+#pragma unroll
+        for (int b = 0; b < 4; b++) {
+          uint32_t const byte = (v >> (8 * b)) & 0xFFu;
+          q[2 * b] = (int)(byte >> 4);      // even idx = high nibble (decompress_kernels.cu:44)
+          q[2 * b + 1] = (int)(byte & 0xFu); // odd idx = low nibble (:48)
+        }
+      } else {
+        uint2 const v = *reinterpret_cast<uint2 const *>(blob + idx);
+#pragma unroll
+        for (int b = 0; b < 4; b++) {
+          q[b] = (int)((v.x >> (8 * b)) & 0xFFu);
+          q[4 + b] = (int)((v.y >> (8 * b)) & 0xFFu);
+        }
+      }
+      T res[8];
+#pragma unroll
+      for (int e = 0; e < 8; e++) {
+        res[e] = dq_elem(q[e], coef[e]);
+      }
+      *reinterpret_cast<uint4 *>(out + idx) = *reinterpret_cast<uint4 *>(res);
+    }
+  }
+}
+
+template <int BITS>
+static int launch_dequant(void const *blob, void *out, int in_dim, int out_dim, int dtype, cudaStream_t s) {
+  FFB_REQUIRE(blob && out, "null argument");
+  FFB_REQUIRE(in_dim > 0 && out_dim > 0 && in_dim % 8 == 0 && out_dim % 32 == 0,
+              "dequant needs in_dim %% 8 == 0 and out_dim %% 32 == 0 (got %d x %d)", in_dim, out_dim);
+  FFB_REQUIRE(dtype == FFB_DT_HALF || dtype == FFB_DT_BF16, "dtype %d not supported", dtype);
+  size_t const total = (size_t)(out_dim / 32) * (in_dim / 8);
+  int blocks = (int)((total + 255) / 256);
+  int const cap = kNumSMs * 8;
+  blocks = blocks > cap ? cap : blocks;
+  if (dtype == FFB_DT_HALF) {
+    dequant_kernel<__half, BITS><<<blocks, 256, 0, s>>>((uint8_t const *)blob, (__half *)out, in_dim, out_dim);
+  } else {
+    dequant_kernel<__nv_bfloat16, BITS><<<blocks, 256, 0, s>>>((uint8_t const *)blob, (__nv_bfloat16 *)out, in_dim, out_dim);
+  }
+  FFB_LAUNCH_CHECK();
+  return FFB_OK;
+}
+
+} // namespace ffb
+
+extern "C" {
+
+size_t ffb_quant_blob_bytes(int quant_type, int dtype, int in_dim, int out_dim) {
+  (void)dtype; // both supported DTs are 2 bytes
+  size_t const n = (size_t)in_dim * out_dim;
+  size_t const values = quant_type == FFB_DT_INT4 ? n / 2 : (quant_type == FFB_DT_INT8 ? n : 0);
+  return values ? values + 2 * (n / 32) * 2 : 0;
+}
+int ffb_dequant_int4(void const *blob, void *out, int in_dim, int out_dim, int dtype, ffb_stream_t stream) {
+  return ffb::launch_dequant<4>(blob, out, in_dim, out_dim, dtype, (cudaStream_t)stream);
+}
+int ffb_dequant_int8(void const *blob, void *out, int in_dim, int out_dim, int dtype, ffb_stream_t stream) {
+  return ffb::launch_dequant<8>(blob, out, in_dim, out_dim, dtype, (cudaStream_t)stream);
+}
+
+} // extern "C"

@@ -1,0 +1,220 @@
+// linear_stream.cu — weight-streaming projection GEMM for small token counts (decode: M <= 64).
+// Replaces Kernels::Linear::forward_kernel (src/ops/kernels/linear_kernels.cu:450-582) for the
+// bandwidth-bound case: at M = 16 the cuBLAS call is a stream over the weights, so the kernel is
+// built around 128-bit coalesced weight loads (8 warps sweep 512 contiguous bytes of each weight
+// row), with the tokens as the M=16 operand of mma.sync m16n8k16 (fp32 accumulate; the reference
+// accumulates in DT).  int8/int4 weights (decompress_kernels.cu:27-70 format) are dequantised in
+// registers right before the MMA with the bit-exact rule of dequant.cuh — the dense matrix is never
+// written to HBM, and the reference's per-forward H2D copy + full decompress pass disappears.
+// A block owns NT*8 consecutive output features (inside one 32-row quantisation group, so all its
+// warps share scale/offset columns); its 8 warps split K in interleaved chunks and are summed in a
+// fixed order through shared memory (deterministic).
+#include "dequant.cuh"
+
+namespace ffb {
+namespace {
+
+template <typename T>
+__device__ __forceinline__ void mma16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                         uint32_t b0, uint32_t b1);
+template <>
+__device__ __forceinline__ void mma16816<__half>(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2,
+                                                 uint32_t a3, uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+template <>
+__device__ __forceinline__ void mma16816<__nv_bfloat16>(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2,
+                                                        uint32_t a3, uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+__device__ __forceinline__ uint32_t word(uint4 const &u, int i) {
+  return i == 0 ? u.x : (i == 1 ? u.y : (i == 2 ? u.z : u.w));
+}
+template <typename T> __device__ __forceinline__ uint32_t pack2(T a, T b) {
+  return (uint32_t)(*reinterpret_cast<unsigned short *>(&a)) | ((uint32_t)(*reinterpret_cast<unsigned short *>(&b)) << 16);
+}
+
+constexpr int LS_WARPS = 8;
+
+// QB: 0 = DT weights, 8 = int8 blob, 4 = int4 blob.  The k -> mma-slot assignment is a fixed
+// permutation applied identically to A and B (a dot product is order-free), chosen so every lane
+// reads 16 contiguous bytes of a weight row.
+template <typename T, int QB, int NT, int MT>
+__global__ void __launch_bounds__(LS_WARPS * 32)
+linear_stream_kernel(T const *__restrict__ A, uint8_t const *__restrict__ W, T const *__restrict__ bias,
+                     T *__restrict__ out, int M, int K, int N) {
+  constexpr int KE = QB == 0 ? 8 : (QB == 8 ? 16 : 32); // k elements per lane per chunk (16 B of weights)
+  constexpr int KC = 4 * KE;                            // k elements per warp chunk
+  constexpr int STEPS = KE / 4;                         // mma k-steps per chunk
+  constexpr int AP = KE / 8;                            // 16-byte activation pieces per row per chunk
+  int const n0 = blockIdx.x * (NT * 8);
+  int const tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  int const g = lane >> 2, tq = lane & 3;
+
+  size_t const value_size = (size_t)K * N;
+  size_t const nvalue_bytes = QB == 4 ? value_size / 2 : value_size;
+  T const *offs = reinterpret_cast<T const *>(W + nvalue_bytes);
+  T const *scales = offs + value_size / 32;
+  size_t const meta_row = (size_t)(n0 / 32) * K;
+
+  float acc[MT][NT][4];
+#pragma unroll
+  for (int mt = 0; mt < MT; mt++) {
+#pragma unroll
+    for (int nt = 0; nt < NT; nt++) {
+      acc[mt][nt][0] = acc[mt][nt][1] = acc[mt][nt][2] = acc[mt][nt][3] = 0.f;
+    }
+  }
+
+  int const nchunks = K / KC;
+#pragma unroll 2
+  for (int kc = warp; kc < nchunks; kc += LS_WARPS) {
+    int const k = kc * KC + tq * KE;
+    uint4 w[NT];
+#pragma unroll
+    for (int nt = 0; nt < NT; nt++) {
+      size_t const e = (size_t)(n0 + nt * 8 + g) * K + k;
+      w[nt] = ldg_stream(QB == 0 ? W + e * 2 : (QB == 8 ? W + e : W + e / 2));
+    }
+    uint4 sc[QB == 0 ? 1 : AP], of[QB == 0 ? 1 : AP];
+    if (QB != 0) {
+#pragma unroll
+      for (int p = 0; p < AP; p++) {
+        sc[p] = *reinterpret_cast<uint4 const *>(scales + meta_row + k + p * 8);
+        of[p] = *reinterpret_cast<uint4 const *>(offs + meta_row + k + p * 8);
+      }
+    }
+    uint4 alo[MT][AP], ahi[MT][AP];
+#pragma unroll
+    for (int mt = 0; mt < MT; mt++) {
+      int const r0 = mt * 16 + g, r1 = r0 + 8;
+#pragma unroll
+      for (int p = 0; p < AP; p++) {
+        alo[mt][p] = r0 < M ? *reinterpret_cast<uint4 const *>(A + (size_t)r0 * K + k + p * 8) : make_uint4(0, 0, 0, 0);
+        ahi[mt][p] = r1 < M ? *reinterpret_cast<uint4 const *>(A + (size_t)r1 * K + k + p * 8) : make_uint4(0, 0, 0, 0);
+      }
+    }
+#pragma unroll
+    for (int s = 0; s < STEPS; s++) {
+      int const p = (4 * s) / 8, wi = ((4 * s) % 8) / 2; // activation piece / 32-bit word of elements 4s..4s+3
+      uint32_t b0[NT], b1[NT];
+      if (QB == 0) {
+#pragma unroll
+        for (int nt = 0; nt < NT; nt++) {
+          b0[nt] = word(w[nt], 2 * s);
+          b1[nt] = word(w[nt], 2 * s + 1);
+        }
+      } else {
+        typename DqCoef<T>::type cf[4];
+        T const *ps = reinterpret_cast<T const *>(&sc[p]);
+        T const *po = reinterpret_cast<T const *>(&of[p]);
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+          cf[e] = dq_coef(ps[(4 * s) % 8 + e], po[(4 * s) % 8 + e]);
+        }
+#pragma unroll
+        for (int nt = 0; nt < NT; nt++) {
+          int q0, q1, q2, q3;
+          if (QB == 8) {
+            uint32_t const v = word(w[nt], s);
+            q0 = v & 0xFF; q1 = (v >> 8) & 0xFF; q2 = (v >> 16) & 0xFF; q3 = v >> 24;
+          } else {
+            uint32_t const v = (word(w[nt], s / 2) >> (16 * (s & 1))) & 0xFFFFu;
+            q0 = (v >> 4) & 0xF; q1 = v & 0xF; q2 = (v >> 12) & 0xF; q3 = (v >> 8) & 0xF;
+          }
+          b0[nt] = pack2<T>(dq_elem(q0, cf[0]), dq_elem(q1, cf[1]));
+          b1[nt] = pack2<T>(dq_elem(q2, cf[2]), dq_elem(q3, cf[3]));
+        }
+      }
+#pragma unroll
+      for (int mt = 0; mt < MT; mt++) {
+        uint32_t const a0 = word(alo[mt][p], wi), a2 = word(alo[mt][p], wi + 1);
+        uint32_t const a1 = word(ahi[mt][p], wi), a3 = word(ahi[mt][p], wi + 1);
+#pragma unroll
+        for (int nt = 0; nt < NT; nt++) {
+          mma16816<T>(acc[mt][nt], a0, a1, a2, a3, b0[nt], b1[nt]);
+        }
+      }
+    }
+  }
+
+  // fixed-order sum over the 8 k-slices
+  __shared__ float tile[MT * 16][NT * 8 + 1];
+  for (int wsel = 0; wsel < LS_WARPS; wsel++) {
+    if (warp == wsel) {
+#pragma unroll
+      for (int mt = 0; mt < MT; mt++) {
+#pragma unroll
+        for (int nt = 0; nt < NT; nt++) {
+#pragma unroll
+          for (int e = 0; e < 4; e++) {
+            int const r = mt * 16 + g + (e >> 1) * 8, c = nt * 8 + 2 * tq + (e & 1);
+            tile[r][c] = wsel == 0 ? acc[mt][nt][e] : tile[r][c] + acc[mt][nt][e];
+          }
+        }
+      }
+    }
+    __syncthreads();
+  }
+  constexpr int SEGS = NT; // 8-column (16 B) segments per row
+  if (tid < MT * 16 * SEGS) {
+    int const r = tid / SEGS, sgm = tid % SEGS;
+    if (r < M) {
+      float v[8];
+#pragma unroll
+      for (int e = 0; e < 8; e++) {
+        v[e] = tile[r][sgm * 8 + e];
+        if (bias) {
+          v[e] += DT<T>::to_f(bias[n0 + sgm * 8 + e]);
+        }
+      }
+      *reinterpret_cast<uint4 *>(out + (size_t)r * N + n0 + sgm * 8) = pack8<T>(v);
+    }
+  }
+}
+
+} // namespace
+
+// M <= 64 rows of `in` starting at row m0.  Returns FFB_OK or an error.
+int launch_linear_stream(int dtype, int quant, void const *in, void *out, void const *w, void const *bias, int M,
+                         int K, int N, cudaStream_t s) {
+  int const KC = quant == FFB_DT_NONE ? 32 : (quant == FFB_DT_INT8 ? 64 : 128);
+  FFB_REQUIRE(K % KC == 0 && N % 32 == 0, "linear_stream needs in_dim %% %d == 0 and out_dim %% 32 == 0", KC);
+  FFB_REQUIRE(M >= 1 && M <= 64, "linear_stream handles 1..64 rows, got %d", M);
+  int const MT = M <= 16 ? 1 : (M <= 32 ? 2 : 4);
+  int const NT = (N / 32 >= 2 * kNumSMs) ? 4 : 2;
+  dim3 grid(N / (NT * 8));
+#define FFB_LS(TT, QB, NTv, MTv)                                                                             \
+  linear_stream_kernel<TT, QB, NTv, MTv><<<grid, LS_WARPS * 32, 0, s>>>((TT const *)in, (uint8_t const *)w, \
+                                                                         (TT const *)bias, (TT *)out, M, K, N)
+#define FFB_LS_MT(TT, QB, NTv)                                         \
+  do {                                                                 \
+    if (MT == 1) FFB_LS(TT, QB, NTv, 1);                               \
+    else if (MT == 2) FFB_LS(TT, QB, NTv, 2);                          \
+    else FFB_LS(TT, QB, NTv, 4);                                       \
+  } while (0)
+#define FFB_LS_NT(TT, QB)                                              \
+  do {                                                                 \
+    if (NT == 4) FFB_LS_MT(TT, QB, 4); else FFB_LS_MT(TT, QB, 2);      \
+  } while (0)
+#define FFB_LS_Q(TT)                                                   \
+  do {                                                                 \
+    if (quant == FFB_DT_NONE) FFB_LS_NT(TT, 0);                        \
+    else if (quant == FFB_DT_INT8) FFB_LS_NT(TT, 8);                   \
+    else FFB_LS_NT(TT, 4);                                             \
+  } while (0)
+  if (dtype == FFB_DT_HALF) {
+    FFB_LS_Q(__half);
+  } else {
+    FFB_LS_Q(__nv_bfloat16);
+  }
+  FFB_LAUNCH_CHECK();
+  return FFB_OK;
+}
+
+} // namespace ffb

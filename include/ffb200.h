@@ -1,0 +1,174 @@
+/* ffb200.h — C ABI of the B200-native FlexFlow Serve attention hot path.
+ *
+ * Every entry point returns an int status (FFB_OK == 0), takes the CUDA stream explicitly as an
+ * opaque pointer (cudaStream_t), never allocates on the hot call and never aborts; the reference
+ * equivalents assert()/exit() instead (include/flexflow/utils/cuda_helper.h:12-60).
+ * All pointers named *_dev are device pointers; *_host are host pointers.
+ *
+ * Each function cites the reference interface it replaces (paths under /root/reference).
+ * The reference-side binding a FlexFlow maintainer would add is shown in INTEGRATION.md.
+ */
+#ifndef FFB200_H
+#define FFB200_H
+
+#include "ffb200_batch_config.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FFB_OK 0
+#define FFB_ERR_INVALID 1     /* bad argument / unsupported shape */
+#define FFB_ERR_CUDA 2        /* a CUDA runtime call failed; see ffb_last_error() */
+#define FFB_ERR_UNSUPPORTED 3 /* feature outside the hot path (e.g. PEFT backward) */
+#define FFB_ERR_NCCL 4
+#define FFB_ERR_STATE 5       /* call order violated (e.g. commit without a previous verify batch) */
+
+typedef void *ffb_stream_t; /* cudaStream_t */
+
+/* Human-readable description of the last failure on the calling thread. */
+char const *ffb_last_error(void);
+/* Library/ABI version and build info ("sm_100a", nvcc version). */
+char const *ffb_version(void);
+/* Device sanity check: FFB_OK only on compute capability 10.x. There is no CPU fallback. */
+int ffb_check_device(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Attention operator state.  Plays the role of IncMultiHeadSelfAttentionMeta /
+ * TreeIncMultiHeadSelfAttentionMeta / SpecIncMultiHeadSelfAttentionMeta
+ * (include/flexflow/ops/inc_multihead_self_attention.h:139-202, ctor
+ * src/ops/inc_multihead_self_attention.cu:1621-1807): owns the KV cache, the previous verify
+ * batch's K/V (for commit) and split-KV scratch.  Head counts are the LOCAL (per TP shard) ones,
+ * as computed in src/ops/inc_multihead_self_attention.cc:516-519.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  int mode;               /* FFB_INC_DECODING_MODE / FFB_BEAM_SEARCH_MODE / FFB_TREE_VERIFY_MODE */
+  int dtype;              /* FFB_DT_HALF or FFB_DT_BF16 (FFB_DT_FLOAT: see DESIGN.md) */
+  int num_q_heads;        /* local query heads */
+  int num_kv_heads;       /* local distinct KV heads (q heads per kv head = num_q_heads/num_kv_heads) */
+  int head_dim;           /* qProjSize == kProjSize == vProjSize: 64 or 128 */
+  int global_num_q_heads; /* for ALiBi position bias only */
+  /* RotaryEmbeddingMeta, include/flexflow/inference.h:46-66 */
+  int apply_rotary_embedding;
+  float rope_theta;
+  int rope_llama3; /* rope_type == "llama3" */
+  float rope_factor;
+  float rope_low_freq_factor;
+  float rope_high_freq_factor;
+  int rope_original_max_position_embeddings;
+  /* FFModel::inc_multihead_self_attention flags, include/flexflow/model.h:738-753 */
+  int scaling_query;
+  float scaling_factor;
+  int qk_prod_scaling;
+  int position_bias;
+  /* BatchConfig::max_requests_per_batch() etc. (src/runtime/batch_config.cc) */
+  int max_requests;
+  int max_sequence_length;
+  int max_spec_tree_tokens; /* 0 in incremental mode; cache rows = max_seq + this */
+  int max_tokens_per_batch;
+} ffb_attn_desc;
+
+typedef struct ffb_attn_s *ffb_attn_t;
+
+/* new IncMultiHeadSelfAttentionMeta(...) — allocates device memory once. */
+int ffb_attn_create(ffb_attn_desc const *desc, ffb_attn_t *out);
+/* ~IncMultiHeadSelfAttentionMeta, inc_multihead_self_attention.cu:1809-1813 */
+int ffb_attn_destroy(ffb_attn_t h);
+/* Bytes of device memory held by the handle (KV cache + scratch). */
+size_t ffb_attn_device_bytes(ffb_attn_t h);
+
+/* Replaces RequestManager::load_batch_config_task (src/runtime/request_manager.cu:83-165):
+ * packs the parts of the host batch descriptor the kernels need into a pinned staging block and
+ * issues ONE cudaMemcpyAsync into the device mirror (the reference issues 2-6 pageable copies).
+ * `bc_host` points at a BatchConfig / TreeVerifyBatchConfig / BeamSearchBatchConfig according
+ * to `mode`.  `staging_pinned_host` must hold sizeof(ffb_combined_batch_config_meta) bytes. */
+int ffb_load_batch_config(void const *bc_host, int mode, void *staging_pinned_host,
+                          ffb_combined_batch_config_meta *meta_dev, ffb_stream_t stream);
+
+/* IncMultiHeadSelfAttention::inference_kernel_wrapper
+ * (include/flexflow/ops/inc_multihead_self_attention.h:115-119,
+ *  src/ops/inc_multihead_self_attention.cu:944-985,1501-1539).
+ * qkv_dev: [num_tokens][3][num_q_heads*head_dim] = [Q | K | V] per token, K/V at q-head granularity
+ * out_dev: [num_tokens][num_q_heads*head_dim]. */
+int ffb_inc_attn_forward(ffb_attn_t h, ffb_batch_config const *bc_host,
+                         ffb_combined_batch_config_meta const *meta_dev, int shard_id,
+                         void const *qkv_dev, void *out_dev, ffb_stream_t stream);
+
+/* TreeIncMultiHeadSelfAttention::inference_kernel_wrapper
+ * (include/flexflow/ops/tree_inc_multihead_self_attention.h:104-108,
+ *  src/ops/tree_inc_multihead_self_attention.cu:575-626): commit accepted tokens of the previous
+ * verify batch, RoPE, append the tree tokens' K/V, tree-masked attention. */
+int ffb_tree_attn_forward(ffb_attn_t h, ffb_tree_verify_batch_config const *bc_host,
+                          ffb_combined_batch_config_meta const *meta_dev, int shard_id,
+                          void const *qkv_dev, void *out_dev, ffb_stream_t stream);
+
+/* SpecIncMultiHeadSelfAttention::inference_kernel_wrapper
+ * (include/flexflow/ops/spec_inc_multihead_self_attention.h:101-106,
+ *  src/ops/spec_inc_multihead_self_attention.cu:681-724). */
+int ffb_spec_attn_forward(ffb_attn_t h, ffb_beam_search_batch_config const *bc_host,
+                          ffb_combined_batch_config_meta const *meta_dev, int shard_id,
+                          void const *qkv_dev, void *out_dev, ffb_stream_t stream);
+
+/* Test/diagnostic access to the private KV cache: copies rows [pos0, pos0+n) of request slot
+ * `request` into k_out_dev/v_out_dev as [n][num_kv_heads][head_dim] (reference cache order,
+ * src/ops/inc_multihead_self_attention.cu:1693-1712), or writes them from that layout. */
+int ffb_attn_read_kv(ffb_attn_t h, int request, int pos0, int n, void *k_out_dev, void *v_out_dev,
+                     ffb_stream_t stream);
+int ffb_attn_write_kv(ffb_attn_t h, int request, int pos0, int n, void const *k_in_dev,
+                      void const *v_in_dev, ffb_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Weight decompression.  Kernels::decompress_int4_general_weights / decompress_int8_general_weights
+ * (src/ops/kernels/decompress_kernels.cu:27-70; launch src/ops/kernels/linear_kernels.cu:469-490).
+ * blob layout: [values | offsets | scales]; element idx = o*in_dim + i; group = (o/32)*in_dim + i;
+ * int4: byte idx/2, even idx = high nibble; w = DT(q) / scale + offset in DT arithmetic.
+ * out_dev: [out_dim][in_dim] DT.  dtype: FFB_DT_HALF (bit-exact with the reference) or FFB_DT_BF16.
+ * ------------------------------------------------------------------------------------------ */
+size_t ffb_quant_blob_bytes(int quant_type, int dtype, int in_dim, int out_dim);
+int ffb_dequant_int4(void const *blob_dev, void *out_dev, int in_dim, int out_dim, int dtype,
+                     ffb_stream_t stream);
+int ffb_dequant_int8(void const *blob_dev, void *out_dev, int in_dim, int out_dim, int dtype,
+                     ffb_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Linear forward (QKV / o_proj dense layers).  Kernels::Linear::forward_kernel_wrapper /
+ * inference_kernel_wrapper (src/ops/kernels/linear_kernels.cu:133-140,187-195,450-582):
+ * out[batch][out_dim] = in[batch][in_dim] * W^T (+ bias), W stored [out_dim][in_dim] (in fastest).
+ * quant_type FFB_DT_NONE: weight_dev is DT; FFB_DT_INT8 / FFB_DT_INT4: weight_dev is the blob
+ * above, dequantised on chip inside the GEMM (never materialised in HBM).
+ * Accumulation is fp32 (the reference accumulates in DT, linear_kernels.cu:507-528).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  int dtype;      /* FFB_DT_HALF / FFB_DT_BF16 */
+  int quant_type; /* FFB_DT_NONE / FFB_DT_INT8 / FFB_DT_INT4 */
+  int in_dim;
+  int out_dim;
+  int max_batch;  /* BatchConfig::max_tokens_per_batch() */
+  int activation; /* 0 = AC_MODE_NONE (only mode on this path) */
+} ffb_linear_desc;
+typedef struct ffb_linear_s *ffb_linear_t;
+int ffb_linear_create(ffb_linear_desc const *desc, ffb_linear_t *out);
+int ffb_linear_destroy(ffb_linear_t h);
+int ffb_linear_forward(ffb_linear_t h, void const *in_dev, void *out_dev, void const *weight_dev,
+                       void const *bias_dev, int batch, ffb_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * AllReduce parallel op.  Kernels::AllReduce::inference_kernel_wrapper
+ * (src/parallel_ops/kernels/allreduce_kernels.cu:56-78): sum over TP shards of
+ * num_active_tokens*hidden elements.  Communicator setup replaces
+ * src/runtime/model.cc:584-628 (ncclGetUniqueId task + ncclCommInitRank index task).
+ * ------------------------------------------------------------------------------------------ */
+#define FFB_NCCL_UNIQUE_ID_BYTES 128
+typedef struct ffb_comm_s *ffb_comm_t;
+int ffb_comm_get_unique_id(void *id_out_128B);
+int ffb_comm_init_rank(void const *id_128B, int nranks, int rank, ffb_comm_t *out);
+int ffb_comm_destroy(ffb_comm_t c);
+/* Adopt an ncclComm_t the runtime already owns (FFHandler.ncclComm, include/flexflow/config.h:110). */
+int ffb_comm_from_nccl(void *nccl_comm, int nranks, int rank, ffb_comm_t *out);
+int ffb_allreduce(ffb_comm_t c, void const *in_dev, void *out_dev, size_t count, int dtype,
+                  ffb_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FFB200_H */
