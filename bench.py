@@ -1,0 +1,354 @@
+#!/usr/bin/env python
+"""bench.py — decode tokens/s of the FlexFlow Serve attention hot path on LLaMA-2-7B shapes.
+
+Workload (BASELINE.json configs[1]): LLaMA-2-7B fp16 incremental decoding, batch 16, 2048-token
+context.  One "step" = one decode step of the hot path over all 32 layers:
+    qkv_proj dense (M=16) -> IncMultiHeadSelfAttention (RoPE, KV append, decode attention) -> o_proj dense
+    [-> AllReduce when TP > 1]
+(the MLP / norms / sampling are outside the path).  N GPUs = tensor parallelism N: heads are
+sharded, total work is fixed ("strong" scaling).  Weights are random-init, KV caches synthetic.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+HIDDEN, NQ, NKV, DH, LAYERS = 4096, 32, 32, 128, 32
+BATCH, CTX = 16, 2048
+METRIC = "decode tok/s + attn HBM GB/s %peak, LLaMA-2-7B tree-verify, TP=1/2/4/8"
+WORKLOAD = "LLaMA-2-7B fp16 incremental decoding, batch 16, 2048-token context (hot path: qkv_proj+attention+o_proj x32 layers)"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        super().__init__(daemon=True)
+        self.gpu, self.rows, self._stop_evt, self.proc = gpu_index, [], threading.Event(), None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([x.strip() for x in line.split(",")])
+                if self._stop_evt.is_set():
+                    break
+        except Exception:
+            pass
+
+    def stop(self):
+        self._stop_evt.set()
+        if self.proc:
+            self.proc.terminate()
+        sm = sorted(int(float(r[1])) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit())
+        mx = [int(float(r[2])) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 9:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx[0] if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def decode_batch():
+    import ffb_testlib as TL
+    return TL.make_inc_batch([dict(slot=s, first_depth=CTX - 1, ntok=1) for s in range(BATCH)])
+
+
+def attn_algorithmic_bytes(n_q_local, n_kv_local):
+    """K+V read once + QKV in + out + KV append, per layer per GPU."""
+    elt = 2
+    kv = 2 * BATCH * CTX * n_kv_local * DH * elt
+    qkv_in = BATCH * (n_q_local + 2 * n_kv_local) * DH * elt
+    out = BATCH * n_q_local * DH * elt
+    append = 2 * BATCH * n_kv_local * DH * elt
+    return kv + qkv_in + out + append
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from flexflow_b200 import batch_config as B
+    from flexflow_b200 import ops
+    from flexflow_b200.model import FFConfig, FFModel
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d (launch with torch.distributed.run)" % (args.gpus, world))
+    torch.cuda.set_device(local_rank)
+    dev = "cuda:%d" % local_rank
+    comm = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(dev))
+
+        def bcast(b):
+            obj = [b]
+            dist.broadcast_object_list(obj, src=0)
+            return obj[0]
+        comm = ops.Communicator(rank, world, bcast)
+    tp = world
+    nq_l, nkv_l = NQ // tp, max(1, NKV // tp)
+    H_l = nq_l * DH
+
+    cfg = FFConfig(data_type=torch.float16, tensor_parallelism_degree=tp, tp_rank=rank, max_requests_per_batch=BATCH,
+                   max_tokens_per_batch=BATCH, max_sequence_length=CTX, device=dev)
+    model = FFModel(cfg, comm)
+    t_in = model.create_tensor(HIDDEN)
+    t = t_in
+    rope = ops.RotaryEmbeddingMeta(apply_rotary_embedding=True, rope_theta=10000.0)
+    for i in range(LAYERS):  # inference/models/llama.cc:94-196 (attention part of the block)
+        qkv = model.dense(t, 3 * H_l, name="layers.%d.self_attn.qkv_proj" % i)
+        a = model.inc_multiquery_self_attention(qkv, HIDDEN, NQ, NKV, rotary_embedding_meta=rope,
+                                                name="layers.%d.self_attn" % i)
+        t = model.dense(a, HIDDEN, name="layers.%d.self_attn.o_proj" % i)
+    model.compile_inference()
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    kfill = torch.randn(CTX - 1, nkv_l, DH, generator=g, device=dev, dtype=torch.float16)
+    vfill = torch.randn(CTX - 1, nkv_l, DH, generator=g, device=dev, dtype=torch.float16)
+    attn_metas = []
+    for lyr in model.layers:
+        if lyr.op_type == "linear":
+            in_dim, out_dim = lyr.inputs[0].dim, lyr.output.dim
+            std = (1.0 / in_dim) ** 0.5 * (8.0 if lyr.name.endswith("o_proj") else 1.0)
+            lyr.weight = (torch.randn(out_dim, in_dim, generator=g, device=dev, dtype=torch.float32) * std).half()
+        elif lyr.op_type == "inc_attn":
+            attn_metas.append(lyr.meta)
+            for s in range(BATCH):
+                lyr.meta.write_kv(s, 0, kfill, vfill)
+    bc = decode_batch()
+    hidden_host = torch.randn(BATCH, HIDDEN, dtype=torch.float16).pin_memory()
+    hidden = hidden_host.to(dev)
+    result_host = torch.empty(BATCH, HIDDEN, dtype=torch.float16).pin_memory()
+    torch.cuda.synchronize()
+
+    def step(upload=False):
+        return model.inference(bc, t_in, hidden, upload=upload)
+
+    model.handler.load_batch_config(bc)
+    for _ in range(max(args.warmup, 3)):
+        out = step()
+    torch.cuda.synchronize()
+    assert torch.isfinite(out.float()).all(), "non-finite hot-path output"
+
+    graph = None
+    if not args.no_graph:
+        try:
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                out = step()
+            graph.replay()
+            torch.cuda.synchronize()
+        except Exception as e:  # keep measuring eagerly, say so
+            print("[bench] CUDA graph capture failed (%s); timing eager launches" % e, file=sys.stderr)
+            graph = None
+            torch.cuda.synchronize()
+
+    def run_step():
+        if graph is not None:
+            graph.replay()
+        else:
+            step()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world > 1:
+            tt = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            return float(tt.item())
+        return ms
+
+    # ---- timed region 1: device-resident inputs --------------------------------------------------
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+        time.sleep(0.3)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        run_step()
+    e1.record()
+    barrier()
+    ms_dev = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+
+    # ---- timed region 2: end to end through the public API with host buffers ----------------------
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        hidden.copy_(hidden_host, non_blocking=True)      # H2D of this step's inputs (pinned)
+        model.handler.load_batch_config(bc)               # H2D of the batch descriptor (pinned staging)
+        run_step()
+        result_host.copy_(out, non_blocking=True)         # D2H of the step's result
+    e1.record()
+    barrier()
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    clocks = sampler.stop() if sampler else None
+    h2d = BATCH * HIDDEN * 2 + B.CombinedBatchConfigMeta.beamTokenInfo.offset
+    d2h = BATCH * HIDDEN * 2
+
+    # ---- roofline of the dominant kernel (decode attention), timed live with CUDA events ----------
+    for m in attn_metas:
+        m.set_profiling(True)
+    kms = []
+    for _ in range(min(args.steps, 10)):
+        step()
+        torch.cuda.synchronize()
+        kms.extend(m.last_kernel_ms() for m in attn_metas)
+    for m in attn_metas:
+        m.set_profiling(False)
+    k_ms = sum(kms) / len(kms)
+    # algorithmic bytes of the decode kernel's launch: K+V rows read once + q in + partial/out write
+    alg = attn_algorithmic_bytes(nq_l, nkv_l)
+    peak, peak_kind = peaks()
+    achieved = alg / (k_ms * 1e-3) / 1e9
+
+    line = {
+        "metric": METRIC, "value": BATCH / (ms_dev * 1e-3), "unit": "tokens/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "batch": BATCH, "context": CTX, "layers": LAYERS, "parallelism": "tp%d" % tp,
+                   "l2_policy": "inputs larger than L2 (17 GB of KV + 4.3 GB of weights stream per step)",
+                   "cuda_graph": graph is not None},
+        "e2e": {"value": BATCH / (ms_e2e * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": ms_e2e},
+        "gpu_launches": args.steps * LAYERS * 5,
+        "clocks": clocks,
+        "roofline": {"kernel": "decode_attn_kernel<half,128,4>", "bound": "hbm", "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_kind, "traffic": None,
+                     "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg,
+                     "attn_share_of_step": k_ms * LAYERS / ms_dev},
+    }
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(max_seconds=25.0)
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+class CpuLayer:
+    """One transformer layer's hot path on the CPU oracle (the reference's algorithm restated in C++,
+    oracle/*.cpp), at the SAME batch/context as the GPU workload.  A full step is LAYERS of these."""
+
+    def __init__(self, threads):
+        import numpy as np
+        from flexflow_b200 import batch_config as B
+        from oracle import oracle as O
+        self.np, self.O = np, O
+        O.set_threads(threads)
+        rng = np.random.default_rng(0)
+        self.attn = O.OracleAttn(B.INC_DECODING_MODE, "half", NQ, DH, BATCH, CTX, 0, BATCH)
+        blk = O.round_to_dt(rng.standard_normal((CTX, NQ * DH)).astype(np.float32), "half")
+        for s in range(BATCH):
+            self.attn.kcache[s, :CTX] = blk
+            self.attn.vcache[s, :CTX] = blk[::-1]
+        self.wqkv = O.round_to_dt((rng.standard_normal((3 * HIDDEN, HIDDEN)) * 0.0156).astype(np.float32), "half")
+        self.wo = O.round_to_dt((rng.standard_normal((HIDDEN, HIDDEN)) * 0.0156).astype(np.float32), "half")
+        self.x = O.round_to_dt(rng.standard_normal((BATCH, HIDDEN)).astype(np.float32), "half")
+        self.bc = decode_batch()
+
+    def run(self):
+        O = self.O
+        qkv = O.linear(self.x, self.wqkv, None, "half").reshape(BATCH, 3, HIDDEN)
+        a = self.attn.inc_forward(self.bc, qkv)
+        return O.linear(a, self.wo, None, "half")
+
+
+def cpu_baseline(max_seconds=25.0):
+    threads = os.cpu_count() or 1
+    layer = CpuLayer(threads)
+    layer.run()
+    t0 = time.perf_counter()
+    n = 0
+    while True:
+        layer.run()
+        n += 1
+        dt = time.perf_counter() - t0
+        if dt > max_seconds or n >= 8:
+            break
+    per_layer = dt / n
+    return {"value": BATCH / (per_layer * LAYERS), "unit": "tokens/s", "cores": threads, "kind": "port",
+            "sample": "%d x one layer (qkv_proj+attention+o_proj, batch 16, ctx 2048) of 32, extrapolated x32; "
+                      "C++ oracle port, %d threads; the reference itself cannot be built here (Legion absent)" % (n, threads),
+            "seconds_per_layer": per_layer}
+
+
+def run_reference(args):
+    """--impl reference: the reference's algorithm on the host cores (oracle port; the reference's own
+    build needs Legion, which is not in the tree — SURVEY F4).  Each step = one layer sample, scaled x32."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    layer = CpuLayer(threads)
+    for _ in range(min(args.warmup, 1)):
+        layer.run()
+    steps = max(1, min(args.steps, 6))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        layer.run()
+    per_layer = (time.perf_counter() - t0) / steps
+    ms_step = per_layer * LAYERS * 1e3
+    val = BATCH / (ms_step * 1e-3)
+    sample = ("each step = one layer (qkv_proj+attention+o_proj, batch 16, ctx 2048) timed and scaled x32 layers; "
+              "%d timed samples; C++ oracle port with %d threads" % (steps, threads))
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "tokens/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": min(args.warmup, 1), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "batch": BATCH, "context": CTX, "layers": LAYERS, "parallelism": "cpu"},
+        "cpu_baseline": {"value": val, "unit": "tokens/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

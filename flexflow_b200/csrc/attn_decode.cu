@@ -238,6 +238,9 @@ int launch_decode_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta
   float const scale = d.qk_prod_scaling ? 1.0f / sqrtf((float)d.head_dim) : 1.0f;
   float const scale_log2 = scale * 1.4426950408889634f;
   dim3 grid(nsplit, d.num_q_heads, T);
+  if (h->profiling) {
+    cudaEventRecord(h->ev0, s);
+  }
 #define FFB_DEC(TT, DH)                                                                                   \
   decode_attn_kernel<TT, DH, U><<<grid, kDecodeThreads, 0, s>>>(                                          \
       (TT const *)h->q_buf, (TT const *)h->k_cache, (TT const *)h->v_cache, h->qdesc, h->partial, (TT *)out, \
@@ -248,6 +251,9 @@ int launch_decode_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta
     if (d.head_dim == 128) FFB_DEC(__nv_bfloat16, 128); else FFB_DEC(__nv_bfloat16, 64);
   }
 #undef FFB_DEC
+  if (h->profiling) {
+    cudaEventRecord(h->ev1, s);
+  }
   FFB_LAUNCH_CHECK();
   if (nsplit > 1) {
     return launch_combine(h, out, T, chunk, nsplit, s);

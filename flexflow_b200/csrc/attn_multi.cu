@@ -360,6 +360,9 @@ int launch_multi_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta,
   float const scale = d.qk_prod_scaling ? 1.0f / sqrtf((float)d.head_dim) : 1.0f;
   float const scale_log2 = scale * 1.4426950408889634f;
   dim3 grid(nsplit, d.num_kv_heads * m_tiles, d.max_requests);
+  if (h->profiling) {
+    cudaEventRecord(h->ev0, s);
+  }
 #define FFB_MQ(TT, DH)                                                                                     \
   do {                                                                                                     \
     size_t const smem = (size_t)(BM + 4 * BN) * DH * 2;                                                    \
@@ -379,6 +382,9 @@ int launch_multi_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta,
     if (d.head_dim == 128) FFB_MQ(__nv_bfloat16, 128); else FFB_MQ(__nv_bfloat16, 64);
   }
 #undef FFB_MQ
+  if (h->profiling) {
+    cudaEventRecord(h->ev1, s);
+  }
   FFB_LAUNCH_CHECK();
   if (nsplit > 1) {
     return launch_combine(h, out, T, chunk, nsplit, s);

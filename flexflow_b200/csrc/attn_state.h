@@ -19,6 +19,9 @@ struct ffb_attn_s {
   ffb::QueryDesc *qdesc = nullptr; // [max_tokens]
   float *partial = nullptr;        // split-KV partials
   size_t partial_bytes = 0;
+  // m->profiling (inc_…cu:1510-1538): events around the dominant attention kernel only
+  bool profiling = false;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int num_generation_tokens_cur = 0; // bc->num_generation_tokens of the batch in flight
   int num_active_infr_tokens = 0; // TreeIncMultiHeadSelfAttentionMeta::num_active_infr_tokens
 };

@@ -117,6 +117,10 @@ int ffb_attn_destroy(ffb_attn_t h) {
   if (!h) {
     return FFB_OK;
   }
+  if (h->ev0) {
+    cudaEventDestroy(h->ev0);
+    cudaEventDestroy(h->ev1);
+  }
   cudaError_t e = cudaFree(h->base);
   delete h;
   if (e != cudaSuccess) {
@@ -127,6 +131,23 @@ int ffb_attn_destroy(ffb_attn_t h) {
 }
 
 size_t ffb_attn_device_bytes(ffb_attn_t h) { return h ? h->bytes : 0; }
+
+int ffb_attn_set_profiling(ffb_attn_t h, int enable) {
+  FFB_REQUIRE(h, "null argument");
+  if (enable && !h->ev0) {
+    FFB_CUDA_TRY(cudaEventCreate(&h->ev0));
+    FFB_CUDA_TRY(cudaEventCreate(&h->ev1));
+  }
+  h->profiling = enable != 0;
+  return FFB_OK;
+}
+
+int ffb_attn_last_kernel_ms(ffb_attn_t h, float *ms) {
+  FFB_REQUIRE(h && ms && h->ev0, "profiling was never enabled on this handle");
+  FFB_CUDA_TRY(cudaEventSynchronize(h->ev1));
+  FFB_CUDA_TRY(cudaEventElapsedTime(ms, h->ev0, h->ev1));
+  return FFB_OK;
+}
 
 int ffb_load_batch_config(void const *bc_host, int mode, void *staging, ffb_combined_batch_config_meta *meta_dev,
                           ffb_stream_t stream) {

@@ -77,6 +77,12 @@ int ffb_attn_destroy(ffb_attn_t h);
 /* Bytes of device memory held by the handle (KV cache + scratch). */
 size_t ffb_attn_device_bytes(ffb_attn_t h);
 
+/* m->profiling of the reference (src/ops/inc_multihead_self_attention.cu:1510-1538 records a
+ * cudaEvent pair around the whole wrapper and printf()s): here the pair brackets the dominant
+ * attention kernel only, and the elapsed time of the last forward call is read back explicitly. */
+int ffb_attn_set_profiling(ffb_attn_t h, int enable);
+int ffb_attn_last_kernel_ms(ffb_attn_t h, float *ms_out);
+
 /* Replaces RequestManager::load_batch_config_task (src/runtime/request_manager.cu:83-165):
  * packs the parts of the host batch descriptor the kernels need into a pinned staging block and
  * issues ONE cudaMemcpyAsync into the device mirror (the reference issues 2-6 pageable copies).

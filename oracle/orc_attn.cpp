@@ -14,7 +14,11 @@ struct OrcAttn {
   float theta, factor, low_ff, high_ff;
   int scaling_query, qk_prod_scaling, position_bias, global_nq;
   float scaling_factor;
-  int ref_quirks; // 1: keep the reference's running qk_max across query tokens (tree/spec kernels)
+  // bit 0: keep the reference's running qk_max across query tokens (tree/spec kernels declare it
+  //        outside the qi loop); bit 1: keep the spec prompt loop's skip of prompt requests while
+  //        tokens_previous_requests < num_generation_tokens (spec_…cu:489-492), which leaves those
+  //        tokens' outputs uncomputed in a mixed beam batch.
+  int ref_quirks;
   int num_active_infr_tokens = 0; // TreeIncMultiHeadSelfAttentionMeta::num_active_infr_tokens
   std::vector<float> qkv;         // devQKVProjArray [max_tokens][3][H] (persists across calls)
   std::vector<float> kcache, vcache;
@@ -214,7 +218,7 @@ void *orc_attn_create(int mode, int dt, int nq, int dh, int max_requests, int ma
   m->low_ff = low_ff; m->high_ff = high_ff; m->orig_max_pos = orig_max_pos;
   m->scaling_query = scaling_query; m->scaling_factor = scaling_factor;
   m->qk_prod_scaling = qk_prod_scaling; m->position_bias = position_bias; m->global_nq = global_nq;
-  m->ref_quirks = 1;
+  m->ref_quirks = 3;
   m->qkv.assign((size_t)max_tokens * 3 * m->H, 0.f);
   m->attn_heads.assign((size_t)max_tokens * m->H, 0.f);
   m->kcache.assign((size_t)max_requests * m->cache_len * m->H, 0.f);
@@ -246,16 +250,15 @@ int orc_inc_attn_forward(void *p, ffb_batch_config const *bc, int shard_id, floa
   }
   float scale = attn_scale(m);
   // compute_attention_kernel_generation :902-927, kernel :372-623: grid (heads, generation tokens)
-  for (int request_idx = 0; request_idx < bc->num_generation_tokens; request_idx++) {
+  orc_parallel_for(bc->num_generation_tokens * m.nq, [&](int w) {
+    int request_idx = w / m.nq, h = w % m.nq;
     int slot = bc->requestsInfo[request_idx].batch_config_request_id;
     int tlength = bc->requestsInfo[slot].first_token_depth_in_request +
                   bc->requestsInfo[slot].num_tokens_in_batch;
-    for (int h = 0; h < m.nq; h++) {
-      float qk_max = -FLT_MAX;
-      attend_row(m, &m.qkv[(size_t)request_idx * 3 * m.H + h * m.dh], slot, h, tlength, scale,
-                 [](int) { return true; }, qk_max, &m.attn_heads[(size_t)request_idx * m.H + h * m.dh]);
-    }
-  }
+    float qk_max = -FLT_MAX;
+    attend_row(m, &m.qkv[(size_t)request_idx * 3 * m.H + h * m.dh], slot, h, tlength, scale,
+               [](int) { return true; }, qk_max, &m.attn_heads[(size_t)request_idx * m.H + h * m.dh]);
+  });
   if (bc->num_tokens > bc->num_generation_tokens) { // :974-977
     for (int i = 0; i < m.max_requests; i++) {
       if (bc->request_completed[i] || !bc->requestsInfo[i].prompt_phase) {
@@ -326,7 +329,7 @@ int orc_tree_attn_forward(void *p, ffb_tree_verify_batch_config const *bc, int s
     for (int h = 0; h < m.nq; h++) {
       float qk_max = -FLT_MAX; // declared OUTSIDE the qi loop in the reference (:107)
       for (int qi = 0; qi < qlength; qi++) {
-        if (!m.ref_quirks) {
+        if (!(m.ref_quirks & 1)) {
           qk_max = -FLT_MAX;
         }
         auto vis = [&](int ti) {
@@ -374,7 +377,7 @@ int orc_spec_attn_forward(void *p, ffb_beam_search_batch_config const *bc, int s
       for (int h = 0; h < m.nq; h++) {
         float qk_max = -FLT_MAX; // outside the qi loop (:106)
         for (int qi = 0; qi < tree_branch_num; qi++) {
-          if (!m.ref_quirks) {
+          if (!(m.ref_quirks & 1)) {
             qk_max = -FLT_MAX;
           }
           int query_token = bm.prompt_size + bm.tree_size - 1 - tree_branch_num + qi; // :143-144
@@ -392,7 +395,7 @@ int orc_spec_attn_forward(void *p, ffb_beam_search_batch_config const *bc, int s
       if (bc->request_completed[i] || !bc->requestsInfo[i].prompt_phase ||
           bc->requestsInfo[i].num_tokens_in_batch == 0) {
         continue;
-      } else if (tokens_previous_requests < bc->num_generation_tokens) {
+      } else if ((m.ref_quirks & 2) && tokens_previous_requests < bc->num_generation_tokens) {
         tokens_previous_requests += bc->requestsInfo[i].num_tokens_in_batch;
         continue;
       }

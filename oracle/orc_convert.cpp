@@ -23,3 +23,7 @@ void orc_half_bits_to_float(uint16_t const *x, float *out, size_t n) {
 
 } // extern "C"
 
+
+static int g_orc_threads = 1;
+int orc_threads() { return g_orc_threads; }
+extern "C" void orc_set_threads(int n) { g_orc_threads = n < 1 ? 1 : n; }

@@ -150,8 +150,8 @@ int orc_traverse_verify_tree(int n_in, int const *in_tok, int const *in_depth, i
 // inside cuBLAS; tolerance covers it).
 void orc_linear_forward(float const *in, float const *w, float const *bias, float *out, int batch,
                         int in_dim, int out_dim, int dt) {
-  for (int b = 0; b < batch; b++) {
-    for (int o = 0; o < out_dim; o++) {
+  orc_parallel_for(out_dim, [&](int o) {
+    for (int b = 0; b < batch; b++) {
       double acc = 0.0;
       float const *x = in + (size_t)b * in_dim, *wr = w + (size_t)o * in_dim;
       for (int i = 0; i < in_dim; i++) {
@@ -163,7 +163,7 @@ void orc_linear_forward(float const *in, float const *w, float const *bias, floa
       }
       out[(size_t)b * out_dim + o] = round_dt(v, dt);
     }
-  }
+  });
 }
 
 } // extern "C"
