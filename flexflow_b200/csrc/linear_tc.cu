@@ -1,13 +1,308 @@
-// linear_tc.cu — placeholder until the tcgen05/TMA GEMM lands (next commit): reports "unsupported" so
-// ffb_linear_forward streams the weights in 64-row passes.
+// linear_tc.cu — tcgen05 / TMA projection GEMM for batched prompt / tree tokens (M >= 65).
+// Replaces the cublasGemmEx call of Kernels::Linear::forward_kernel
+// (src/ops/kernels/linear_kernels.cu:507-528): out[M][N] = A[M][K] * W[N][K]^T, both operands K-major.
+// One 128 x BN output tile per CTA: a TMA producer thread streams 128B-swizzled A/W tiles through a
+// STAGES-deep shared-memory ring (mbarrier full/empty pairs), one elected thread issues
+// tcgen05.mma.cta_group::1.kind::f16 (UMMA 128 x BN x 16, fp32 accumulator in TMEM), tcgen05.commit
+// releases ring slots and finally signals the four epilogue warps, which read the accumulator with
+// tcgen05.ld (32 lanes x 32 columns per instruction), add the bias, convert and store.
+// The reference accumulates in DT (cuBLAS compute type = output type); fp32 here.
+// int8/int4 weights at large M are dequantised once per call into a private DT scratch and fed to the
+// same kernel (what the reference does, minus its host-to-device copy); the M <= 64 path
+// (linear_stream.cu) never materialises them.
+#include <cuda.h>
+
+#include <new>
+#include <type_traits>
+
 #include "common.cuh"
+
+extern "C" int ffb_dequant_int4(void const *, void *, int, int, int, ffb_stream_t);
+extern "C" int ffb_dequant_int8(void const *, void *, int, int, int, ffb_stream_t);
+
 namespace ffb {
-struct LinearTcState {};
-int linear_tc_supported(int, int, int, int) { return 0; }
-LinearTcState *linear_tc_create(int, int, int, int, int) { return nullptr; }
-void linear_tc_destroy(LinearTcState *) {}
-int launch_linear_tc(LinearTcState *, int, int, void const *, void *, void const *, void const *, int, int, int, cudaStream_t) {
-  set_error("tcgen05 GEMM not built");
-  return FFB_ERR_UNSUPPORTED;
+namespace {
+
+constexpr int TC_BM = 128, TC_BK = 64, TC_THREADS = 256;
+
+__device__ __forceinline__ uint32_t smem_u32(void const *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
 }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  uint32_t const addr = smem_u32(bar);
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "DONE:\n\t"
+      "}" ::"r"(addr), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void *dst, CUtensorMap const *tm, int c0, int c1, uint64_t *bar) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+               ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t *bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+// K-major operand tile, 128-byte swizzle: rows of 128 B, 8-row groups 1024 B apart
+// (cute::UMMA::SmemDescriptor: start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48), layout [61,64))
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+template <typename T, int BN, int STAGES>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+linear_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 T *__restrict__ out, T const *__restrict__ bias, int M, int N, int K) {
+  constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2, B_BYTES = BN * TC_BK * 2;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], tmem_full_bar;
+  __shared__ uint32_t tmem_base_smem;
+  // 128B-swizzled tiles need 1024-byte alignment
+  uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t *sA = smem, *sB = smem + STAGES * A_BYTES;
+
+  int const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int const n_blk = blockIdx.x, m_blk = blockIdx.y;
+  int const num_k = K / TC_BK;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; s++) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(&tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) { // TMEM: BN fp32 accumulator columns (power of two >= 32)
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "r"((uint32_t)BN));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t const tmem_base = tmem_base_smem;
+
+  if (warp == 0 && lane == 0) {
+    // ===== TMA producer =====
+    for (int kb = 0; kb < num_k; kb++) {
+      int const s = kb % STAGES;
+      uint32_t const ph = (kb / STAGES) & 1;
+      mbar_wait(&empty_bar[s], ph ^ 1);
+      mbar_expect_tx(&full_bar[s], A_BYTES + B_BYTES);
+      tma_load_2d(sA + s * A_BYTES, &tmA, kb * TC_BK, m_blk * TC_BM, &full_bar[s]);
+      tma_load_2d(sB + s * B_BYTES, &tmB, kb * TC_BK, n_blk * BN, &full_bar[s]);
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ===== MMA issuer =====
+    // cute::UMMA::InstrDescriptor: c_format F32 (1) @4, a/b format @7/@10 (F16 0, BF16 1), K-major, N>>3 @17, M>>4 @24
+    constexpr uint32_t fmt = sizeof(T) == 2 && std::is_same<T, __nv_bfloat16>::value ? 1u : 0u;
+    constexpr uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+    for (int kb = 0; kb < num_k; kb++) {
+      int const s = kb % STAGES;
+      uint32_t const ph = (kb / STAGES) & 1;
+      mbar_wait(&full_bar[s], ph);
+      tc_fence_after();
+      uint64_t const da = umma_desc_sw128(smem_u32(sA + s * A_BYTES));
+      uint64_t const db = umma_desc_sw128(smem_u32(sB + s * B_BYTES));
+#pragma unroll
+      for (int k = 0; k < TC_BK / 16; k++) {
+        // advance 16 elements (32 B) along K inside the swizzle atom: start-address field += 2
+        tc_mma_f16(tmem_base, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+      }
+      tc_commit(&empty_bar[s]); // slot reusable once these MMAs have read it
+    }
+    tc_commit(&tmem_full_bar);
+  } else if (warp >= 4) {
+    // ===== epilogue: TMEM -> registers -> global =====
+    mbar_wait(&tmem_full_bar, 0);
+    tc_fence_after();
+    int const q = warp & 3; // this warp may touch TMEM lanes [32q, 32q+32)
+    int const row = m_blk * TC_BM + q * 32 + lane;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 32) {
+      uint32_t r[32];
+      tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
+      if (row < M) {
+        int const col = n_blk * BN + c0;
+        T *dst = out + (size_t)row * N + col;
+#pragma unroll
+        for (int v = 0; v < 4; v++) {
+          float f[8];
+#pragma unroll
+          for (int e = 0; e < 8; e++) {
+            f[e] = __uint_as_float(r[v * 8 + e]);
+            if (bias) {
+              f[e] += DT<T>::to_f(bias[col + v * 8 + e]);
+            }
+          }
+          *reinterpret_cast<uint4 *>(dst + v * 8) = pack8<T>(f);
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)BN));
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, cuuint64_t const *,
+                                  cuuint64_t const *, cuuint32_t const *, cuuint32_t const *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess) {
+      fn = (EncodeTiledFn)p;
+    }
+  }
+  return fn;
+}
+
+// [rows][K] row-major 16-bit matrix, box = 64 (K) x box_rows, 128B swizzle, OOB rows read as zero
+int make_map(CUtensorMap *tm, int dtype, void const *ptr, int rows, int K, int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled is not available from the driver");
+    return FFB_ERR_CUDA;
+  }
+  cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)K * 2};
+  cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(tm, dtype == FFB_DT_HALF ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                  (void *)ptr, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d (ptr %p rows %d K %d)", (int)r, ptr, rows, K);
+    return FFB_ERR_CUDA;
+  }
+  return FFB_OK;
+}
+
+} // namespace
+
+struct LinearTcState {
+  int dtype, quant, K, N, max_batch;
+  void *scratch = nullptr; // dequantised weights [N][K] DT (quantised layers only)
+  bool attr_set[2] = {false, false};
+};
+
+int linear_tc_supported(int dtype, int quant, int K, int N) {
+  (void)quant;
+  if (getenv("FFB_DISABLE_TC")) {
+    return 0;
+  }
+  return (dtype == FFB_DT_HALF || dtype == FFB_DT_BF16) && K % TC_BK == 0 && N % 128 == 0;
+}
+
+LinearTcState *linear_tc_create(int dtype, int quant, int K, int N, int max_batch) {
+  LinearTcState *st = new (std::nothrow) LinearTcState();
+  if (!st) {
+    set_error("out of host memory");
+    return nullptr;
+  }
+  st->dtype = dtype; st->quant = quant; st->K = K; st->N = N; st->max_batch = max_batch;
+  if (quant != FFB_DT_NONE && max_batch > 64) {
+    cudaError_t e = cudaMalloc(&st->scratch, (size_t)K * N * 2);
+    if (e != cudaSuccess) {
+      set_error("cudaMalloc of the dequant scratch failed: %s", cudaGetErrorString(e));
+      delete st;
+      return nullptr;
+    }
+  }
+  return st;
+}
+
+void linear_tc_destroy(LinearTcState *st) {
+  if (st) {
+    if (st->scratch) {
+      cudaFree(st->scratch);
+    }
+    delete st;
+  }
+}
+
+int launch_linear_tc(LinearTcState *st, int dtype, int quant, void const *in, void *out, void const *w,
+                     void const *bias, int M, int K, int N, cudaStream_t s) {
+  void const *wd = w;
+  if (quant != FFB_DT_NONE) {
+    FFB_REQUIRE(st->scratch, "quantised layer created with max_batch <= 64 has no dequant scratch");
+    int rc = quant == FFB_DT_INT4 ? ffb_dequant_int4(w, st->scratch, K, N, dtype, s) : ffb_dequant_int8(w, st->scratch, K, N, dtype, s);
+    if (rc != FFB_OK) {
+      return rc;
+    }
+    wd = st->scratch;
+  }
+  constexpr int BN = 128, STAGES = 6;
+  CUtensorMap tmA, tmB;
+  int rc = make_map(&tmA, dtype, in, M, K, TC_BM);
+  if (rc != FFB_OK) {
+    return rc;
+  }
+  rc = make_map(&tmB, dtype, wd, N, K, BN);
+  if (rc != FFB_OK) {
+    return rc;
+  }
+  size_t const smem = (size_t)STAGES * (TC_BM + BN) * TC_BK * 2 + 1024;
+  dim3 grid(N / BN, (M + TC_BM - 1) / TC_BM);
+  if (dtype == FFB_DT_HALF) {
+    if (!st->attr_set[0]) {
+      FFB_CUDA_TRY(cudaFuncSetAttribute(linear_tc_kernel<__half, BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      st->attr_set[0] = true;
+    }
+    linear_tc_kernel<__half, BN, STAGES><<<grid, TC_THREADS, smem, s>>>(tmA, tmB, (__half *)out, (__half const *)bias, M, N, K);
+  } else {
+    if (!st->attr_set[1]) {
+      FFB_CUDA_TRY(cudaFuncSetAttribute(linear_tc_kernel<__nv_bfloat16, BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      st->attr_set[1] = true;
+    }
+    linear_tc_kernel<__nv_bfloat16, BN, STAGES><<<grid, TC_THREADS, smem, s>>>(tmA, tmB, (__nv_bfloat16 *)out, (__nv_bfloat16 const *)bias, M, N, K);
+  }
+  FFB_LAUNCH_CHECK();
+  return FFB_OK;
+}
+
 } // namespace ffb

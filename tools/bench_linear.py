@@ -1,0 +1,53 @@
+"""Projection GEMM micro-benchmark: TFLOP/s (tcgen05 path) and GB/s (weight-streaming path) at the 7B shapes.
+    python tools/bench_linear.py [--json out.json]"""
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from flexflow_b200 import batch_config as B  # noqa: E402
+from flexflow_b200 import ops  # noqa: E402
+
+
+def time_ms(fn, iters=20, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def main():
+    h = ops.FFHandler("cuda:0")
+    res = []
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    for name, K, N in (("qkv_proj", 4096, 12288), ("o_proj", 4096, 4096)):
+        ws = [(torch.randn(N, K, device="cuda") * 0.02).half() for _ in range(4)]  # rotate weights: > L2
+        for M in (16, 64, 128, 256, 512, 1024):
+            m = ops.LinearMeta(h, K, N, max_tokens_per_batch=1024)
+            x = torch.randn(M, K, device="cuda").half()
+            out = torch.empty(M, N, device="cuda", dtype=torch.float16)
+            i = [0]
+
+            def fn():
+                i[0] += 1
+                ops.Linear.forward_kernel_wrapper(m, x, out, ws[i[0] % 4], None, K, N, M)
+            ms = time_ms(fn)
+            ref = time_ms(lambda: torch.matmul(x, ws[0].t(), out=out))
+            flops = 2.0 * M * K * N
+            res.append(dict(layer=name, M=M, K=K, N=N, ms=ms, tflops=flops / ms / 1e9, weight_gbs=K * N * 2 / ms / 1e6,
+                            cublas_ms=ref, cublas_tflops=flops / ref / 1e9))
+            print(res[-1], flush=True)
+    if "--json" in sys.argv:
+        json.dump(res, open(sys.argv[sys.argv.index("--json") + 1], "w"), indent=1)
+
+
+if __name__ == "__main__":
+    main()
