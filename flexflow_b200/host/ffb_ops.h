@@ -1,0 +1,173 @@
+// ffb_ops.h — C++ host-side mirror of the reference's operator interface for the attention hot path,
+// header-only on top of the C ABI (include/ffb200.h).  Names, argument order and meaning follow the
+// reference so that its op tasks can call these instead of their own wrappers:
+//   IncMultiHeadSelfAttention::inference_kernel_wrapper     include/flexflow/ops/inc_multihead_self_attention.h:115-119
+//   TreeIncMultiHeadSelfAttention::inference_kernel_wrapper include/flexflow/ops/tree_inc_multihead_self_attention.h:104-108
+//   SpecIncMultiHeadSelfAttention::inference_kernel_wrapper include/flexflow/ops/spec_inc_multihead_self_attention.h:101-106
+//   Kernels::Linear::{forward,inference}_kernel_wrapper     src/ops/kernels/linear_kernels.cu:133-140,187-195
+//   Kernels::AllReduce::inference_kernel_wrapper            include/flexflow/parallel_ops/kernels/allreduce_kernels.h:28-31
+// Differences: errors throw ffb::Error instead of assert()/exit(); the CUDA stream is passed explicitly
+// (the reference pulls it from Legion, src/runtime/cuda_helper.cu:18-23).
+#pragma once
+#include <stdexcept>
+#include <string>
+
+#include "../../include/ffb200.h"
+
+namespace ffb {
+
+struct Error : std::runtime_error {
+  int code;
+  Error(int c, std::string const &what) : std::runtime_error(what), code(c) {}
+};
+inline void check(int rc, char const *what) {
+  if (rc != FFB_OK) {
+    throw Error(rc, std::string(what) + ": " + ffb_last_error());
+  }
+}
+
+// include/flexflow/accessor.h:55-87 — {data_type, domain, ptr}; the domain is reduced to what the path reads
+struct GenericTensorAccessorR {
+  int data_type;
+  void const *ptr;
+  size_t hidden_dim; // innermost extent (domain.hi()[0]-domain.lo()[0]+1)
+};
+struct GenericTensorAccessorW {
+  int data_type;
+  void *ptr;
+  size_t hidden_dim;
+};
+
+// include/flexflow/inference.h:46-66
+struct RotaryEmbeddingMeta {
+  bool apply_rotary_embedding = false;
+  float rope_theta = 10000.0f;
+  std::string rope_type = "default";
+  float factor = 8.0f, low_freq_factor = 1.0f, high_freq_factor = 4.0f;
+  int original_max_position_embeddings = 8192;
+};
+
+// The slice of FFHandler the path uses (include/flexflow/config.h:91-113)
+struct FFHandler {
+  ffb_combined_batch_config_meta *batch_config_metadata = nullptr; // device
+  void *staging_pinned = nullptr;                                  // host, pinned, same size
+  ffb_comm_t ncclComm = nullptr;
+  // RequestManager::load_batch_config_task, src/runtime/request_manager.cu:83-165
+  void load_batch_config(void const *bc, int mode, ffb_stream_t stream) const {
+    check(ffb_load_batch_config(bc, mode, staging_pinned, batch_config_metadata, stream), "ffb_load_batch_config");
+  }
+};
+
+// IncMultiHeadSelfAttentionMeta (inc_multihead_self_attention.h:139-202; ctor inc_…cu:1621-1807).
+// _num_q_heads/_num_kv_heads are the per-shard counts (inc_…cc:516-519).
+class IncMultiHeadSelfAttentionMeta {
+public:
+  IncMultiHeadSelfAttentionMeta(FFHandler handler, int infer_mode, int data_type, int head_dim,
+                                RotaryEmbeddingMeta const &rope, bool scaling_query, bool qk_prod_scaling,
+                                bool position_bias, float scaling_factor, int global_num_q_heads, int _num_q_heads,
+                                int _num_kv_heads, int max_requests_per_batch, int max_tokens_per_batch,
+                                int max_sequence_length, int max_spec_tree_token_num)
+      : handle(handler) {
+    ffb_attn_desc d{};
+    d.mode = infer_mode; d.dtype = data_type; d.num_q_heads = _num_q_heads; d.num_kv_heads = _num_kv_heads;
+    d.head_dim = head_dim; d.global_num_q_heads = global_num_q_heads;
+    d.apply_rotary_embedding = rope.apply_rotary_embedding; d.rope_theta = rope.rope_theta;
+    d.rope_llama3 = rope.rope_type == "llama3"; d.rope_factor = rope.factor;
+    d.rope_low_freq_factor = rope.low_freq_factor; d.rope_high_freq_factor = rope.high_freq_factor;
+    d.rope_original_max_position_embeddings = rope.original_max_position_embeddings;
+    d.scaling_query = scaling_query; d.scaling_factor = scaling_factor; d.qk_prod_scaling = qk_prod_scaling;
+    d.position_bias = position_bias; d.max_requests = max_requests_per_batch;
+    d.max_sequence_length = max_sequence_length;
+    d.max_spec_tree_tokens = infer_mode == FFB_INC_DECODING_MODE ? 0 : max_spec_tree_token_num;
+    d.max_tokens_per_batch = max_tokens_per_batch;
+    check(ffb_attn_create(&d, &h_), "ffb_attn_create");
+  }
+  ~IncMultiHeadSelfAttentionMeta() { ffb_attn_destroy(h_); }
+  IncMultiHeadSelfAttentionMeta(IncMultiHeadSelfAttentionMeta const &) = delete;
+  IncMultiHeadSelfAttentionMeta &operator=(IncMultiHeadSelfAttentionMeta const &) = delete;
+  FFHandler handle;
+  bool profiling = false;
+  ffb_attn_t raw() const { return h_; }
+
+private:
+  ffb_attn_t h_ = nullptr;
+};
+using TreeIncMultiHeadSelfAttentionMeta = IncMultiHeadSelfAttentionMeta; // mode = FFB_TREE_VERIFY_MODE
+using SpecIncMultiHeadSelfAttentionMeta = IncMultiHeadSelfAttentionMeta; // mode = FFB_BEAM_SEARCH_MODE
+
+struct IncMultiHeadSelfAttention {
+  static void inference_kernel_wrapper(IncMultiHeadSelfAttentionMeta *m, ffb_batch_config const *bc, int shard_id,
+                                       GenericTensorAccessorR const &input, GenericTensorAccessorW const &output,
+                                       ffb_stream_t stream) {
+    if (input.data_type != output.data_type) {
+      throw Error(FFB_ERR_INVALID, "input/output data types differ"); // assert(input.data_type == output.data_type)
+    }
+    check(ffb_inc_attn_forward(m->raw(), bc, m->handle.batch_config_metadata, shard_id, input.ptr, output.ptr, stream),
+          "ffb_inc_attn_forward");
+  }
+};
+struct TreeIncMultiHeadSelfAttention {
+  static void inference_kernel_wrapper(TreeIncMultiHeadSelfAttentionMeta *m, ffb_tree_verify_batch_config const *bc,
+                                       int shard_id, GenericTensorAccessorR const &input,
+                                       GenericTensorAccessorW const &output, ffb_stream_t stream) {
+    check(ffb_tree_attn_forward(m->raw(), bc, m->handle.batch_config_metadata, shard_id, input.ptr, output.ptr, stream),
+          "ffb_tree_attn_forward");
+  }
+};
+struct SpecIncMultiHeadSelfAttention {
+  static void inference_kernel_wrapper(SpecIncMultiHeadSelfAttentionMeta const *m,
+                                       ffb_beam_search_batch_config const *bc, int shard_id,
+                                       GenericTensorAccessorR const &input, GenericTensorAccessorW const &output,
+                                       ffb_stream_t stream) {
+    check(ffb_spec_attn_forward(m->raw(), bc, m->handle.batch_config_metadata, shard_id, input.ptr, output.ptr, stream),
+          "ffb_spec_attn_forward");
+  }
+};
+
+class LinearMeta {
+public:
+  LinearMeta(FFHandler handler, int data_type, int quantization_type, int in_dim, int out_dim, int max_batch)
+      : handle(handler) {
+    ffb_linear_desc d{data_type, quantization_type, in_dim, out_dim, max_batch, 0};
+    check(ffb_linear_create(&d, &h_), "ffb_linear_create");
+  }
+  ~LinearMeta() { ffb_linear_destroy(h_); }
+  LinearMeta(LinearMeta const &) = delete;
+  LinearMeta &operator=(LinearMeta const &) = delete;
+  FFHandler handle;
+  ffb_linear_t raw() const { return h_; }
+
+private:
+  ffb_linear_t h_ = nullptr;
+};
+
+namespace Kernels {
+namespace Linear {
+inline void forward_kernel_wrapper(LinearMeta const *m, void const *input_ptr, void *output_ptr,
+                                   void const *filter_ptr, void const *bias_ptr, int in_dim, int out_dim,
+                                   int batch_size, ffb_stream_t stream) {
+  (void)in_dim;
+  (void)out_dim;
+  check(ffb_linear_forward(m->raw(), input_ptr, output_ptr, filter_ptr, bias_ptr, batch_size, stream), "ffb_linear_forward");
+}
+inline void inference_kernel_wrapper(LinearMeta *m, ffb_batch_config const *bc, void const *input_ptr,
+                                     void *output_ptr, void const *filter_ptr, void const *bias_ptr, int in_dim,
+                                     int out_dim, int batch_size, ffb_stream_t stream) {
+  (void)bc;
+  forward_kernel_wrapper(m, input_ptr, output_ptr, filter_ptr, bias_ptr, in_dim, out_dim, batch_size, stream);
+}
+} // namespace Linear
+namespace AllReduce {
+struct AllReduceMeta {
+  FFHandler handle;
+};
+inline void inference_kernel_wrapper(AllReduceMeta const *m, ffb_batch_config const *bc,
+                                     GenericTensorAccessorR const &input, GenericTensorAccessorW const &output,
+                                     ffb_stream_t stream) {
+  size_t const num_elements = (size_t)bc->num_tokens * input.hidden_dim; // allreduce_kernels.cu:64-65
+  check(ffb_allreduce(m->handle.ncclComm, input.ptr, output.ptr, num_elements, input.data_type, stream), "ffb_allreduce");
+}
+} // namespace AllReduce
+} // namespace Kernels
+
+} // namespace ffb
