@@ -245,7 +245,7 @@ def run_ours(args):
                 "ms_per_step": ms_e2e},
         "gpu_launches": args.steps * LAYERS * 5,
         "clocks": clocks,
-        "roofline": {"kernel": "decode_attn_kernel<half,128,4>", "bound": "hbm", "achieved": achieved, "peak": peak,
+        "roofline": {"kernel": "decode_attn_kernel<half,128,8>", "bound": "hbm", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_kind, "traffic": None,
                      "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg,
                      "attn_share_of_step": k_ms * LAYERS / ms_dev},

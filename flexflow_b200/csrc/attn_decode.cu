@@ -24,8 +24,8 @@ template <typename T, int DH, int U>
 __global__ void __launch_bounds__(kDecodeThreads)
 decode_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache,
                    T const *__restrict__ v_cache, QueryDesc const *__restrict__ qdesc,
-                   float *__restrict__ partial, T *__restrict__ out, int nq, int nkv, int cache_len,
-                   int chunk, int nsplit, float scale_log2) {
+                   float *__restrict__ partial, int *__restrict__ split_counter, T *__restrict__ out, int nq,
+                   int nkv, int cache_len, int chunk, int nsplit, float scale_log2, int fuse_combine) {
   constexpr int LPK = DH / 8;   // lanes per key row (16-byte slices)
   constexpr int KPW = 32 / LPK; // keys per warp-wide load
   constexpr int GROUPS = kDecodeWarps * KPW;
@@ -34,7 +34,7 @@ decode_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache,
   int const kv_len = qd.kv_len;
   int const k0 = split * chunk;
   if (k0 >= kv_len) {
-    if (kv_len <= 0 && split == 0 && nsplit == 1 && threadIdx.x < DH) {
+    if (kv_len <= 0 && split == 0 && threadIdx.x < DH) {
       out[((size_t)t * nq + head) * DH + threadIdx.x] = DT<T>::from_f(0.f);
     }
     return;
@@ -89,26 +89,27 @@ decode_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache,
       s[u] = (kb + u * KPW + sub < k1) ? d : -INFINITY;
       mx = fmaxf(mx, s[u]);
     }
-    if (mx != -INFINITY) {
-      float const corr = fast_exp2(m - mx); // m == -inf -> 0
-      l *= corr;
+    // branch-free update (a branch here lets the compiler sink the V loads behind the K reduction and
+    // halves the loads in flight): with no visible key yet, mx == -inf and everything below is 0
+    float const base = (mx == -INFINITY) ? 0.f : mx;
+    float const corr = fast_exp2(m - base); // m == -inf -> 0 (l and acc are 0 then)
+    l *= corr;
+#pragma unroll
+    for (int e = 0; e < 8; e++) {
+      acc[e] *= corr;
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      float const p = fast_exp2(s[u] - base); // s == -inf -> 0
+      l += p;
+      float vf[8];
+      unpack8<T>(vr[u], vf);
 #pragma unroll
       for (int e = 0; e < 8; e++) {
-        acc[e] *= corr;
+        acc[e] = fmaf(p, vf[e], acc[e]);
       }
-#pragma unroll
-      for (int u = 0; u < U; u++) {
-        float const p = fast_exp2(s[u] - mx); // s == -inf -> 0
-        l += p;
-        float vf[8];
-        unpack8<T>(vr[u], vf);
-#pragma unroll
-        for (int e = 0; e < 8; e++) {
-          acc[e] = fmaf(p, vf[e], acc[e]);
-        }
-      }
-      m = mx;
     }
+    m = mx;
   }
 
   // merge the GROUPS independent (m, l, acc) streams of this block
@@ -124,6 +125,7 @@ decode_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache,
     s_l[g] = l;
   }
   __syncthreads();
+  __shared__ int s_last;
   if (threadIdx.x < DH) {
     float M = -INFINITY;
 #pragma unroll
@@ -146,6 +148,28 @@ decode_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache,
       if (threadIdx.x == 0) {
         rec[DH] = M;
         rec[DH + 1] = L;
+      }
+    }
+  }
+  if (nsplit > 1 && fuse_combine) {
+    // last-arriving split of this (token, head) merges all records: no separate combine launch
+    int const nvalid = min(nsplit, (kv_len + chunk - 1) / chunk);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      // release/acquire at gpu scope; the bar.sync above makes the other threads' record stores
+      // cumulative with this release, so no per-thread __threadfence is needed
+      int prev;
+      asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], 1;" : "=r"(prev) : "l"(split_counter + t * nq + head) : "memory");
+      s_last = prev == nvalid - 1;
+      if (s_last) {
+        split_counter[t * nq + head] = 0; // self-reset for the next launch
+      }
+    }
+    __syncthreads();
+    if (s_last) {
+      if (threadIdx.x < 32 * (DH / 32)) {
+        combine_record<T, DH>(partial + ((size_t)t * nq + head) * nsplit * (DH + 2), nvalid,
+                              out + ((size_t)t * nq + head) * DH, threadIdx.x, 32 * (DH / 32));
       }
     }
   }
@@ -224,11 +248,11 @@ int launch_decode_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta
   if (T <= 0) {
     return FFB_OK;
   }
-  constexpr int U = 4;
-  int const granule = kDecodeWarps * U * (32 / (d.head_dim / 8));
+  int const U = getenv("FFB_DECODE_U") ? atoi(getenv("FFB_DECODE_U")) : 8; // keys per warp-load group
+  int const granule = kDecodeWarps * 8 * (32 / (d.head_dim / 8));
   int nsplit = 1;
   int chunk = choose_chunk(h, (long)T * d.num_q_heads, kv_len_max < 1 ? 1 : kv_len_max, granule,
-                           (long)kNumSMs * 16, "FFB_DECODE_CHUNK", &nsplit);
+                           (long)kNumSMs * 8, "FFB_DECODE_CHUNK", &nsplit);
   // respect the partial buffer
   size_t const rec = (size_t)(d.head_dim + 2) * sizeof(float);
   while (nsplit > 1 && (size_t)T * d.num_q_heads * nsplit * rec > h->partial_bytes) {
@@ -237,25 +261,33 @@ int launch_decode_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta
   }
   float const scale = d.qk_prod_scaling ? 1.0f / sqrtf((float)d.head_dim) : 1.0f;
   float const scale_log2 = scale * 1.4426950408889634f;
+  int const fuse = getenv("FFB_SEPARATE_COMBINE") ? 0 : 1;
   dim3 grid(nsplit, d.num_q_heads, T);
   if (h->profiling) {
     cudaEventRecord(h->ev0, s);
   }
-#define FFB_DEC(TT, DH)                                                                                   \
-  decode_attn_kernel<TT, DH, U><<<grid, kDecodeThreads, 0, s>>>(                                          \
-      (TT const *)h->q_buf, (TT const *)h->k_cache, (TT const *)h->v_cache, h->qdesc, h->partial, (TT *)out, \
-      d.num_q_heads, d.num_kv_heads, h->cache_len, chunk, nsplit, scale_log2)
+#define FFB_DEC_U(TT, DH, UU)                                                                             \
+  decode_attn_kernel<TT, DH, UU><<<grid, kDecodeThreads, 0, s>>>(                                          \
+      (TT const *)h->q_buf, (TT const *)h->k_cache, (TT const *)h->v_cache, h->qdesc, h->partial, h->split_counter, (TT *)out, \
+      d.num_q_heads, d.num_kv_heads, h->cache_len, chunk, nsplit, scale_log2, fuse)
+#define FFB_DEC(TT, DH)                     \
+  do {                                      \
+    if (U == 8) FFB_DEC_U(TT, DH, 8);       \
+    else if (U == 2) FFB_DEC_U(TT, DH, 2);  \
+    else FFB_DEC_U(TT, DH, 4);              \
+  } while (0)
   if (d.dtype == FFB_DT_HALF) {
     if (d.head_dim == 128) FFB_DEC(__half, 128); else FFB_DEC(__half, 64);
   } else {
     if (d.head_dim == 128) FFB_DEC(__nv_bfloat16, 128); else FFB_DEC(__nv_bfloat16, 64);
   }
 #undef FFB_DEC
+#undef FFB_DEC_U
   if (h->profiling) {
     cudaEventRecord(h->ev1, s);
   }
   FFB_LAUNCH_CHECK();
-  if (nsplit > 1) {
+  if (nsplit > 1 && !fuse) {
     return launch_combine(h, out, T, chunk, nsplit, s);
   }
   return FFB_OK;

@@ -75,8 +75,9 @@ template <typename T, int DH>
 __global__ void __launch_bounds__(MQ_THREADS, 2)
 multi_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache, T const *__restrict__ v_cache,
                   QueryDesc const *__restrict__ qdesc, ffb_combined_batch_config_meta const *__restrict__ meta,
-                  float *__restrict__ partial, T *__restrict__ out, int mode, int nq, int nkv, int cache_len,
-                  int m_tiles, int chunk, int nsplit, float scale_log2, int num_generation_tokens) {
+                  float *__restrict__ partial, int *__restrict__ split_counter, T *__restrict__ out, int mode, int nq,
+                  int nkv, int cache_len, int m_tiles, int chunk, int nsplit, float scale_log2,
+                  int num_generation_tokens, int fuse_combine) {
   constexpr int CPR = DH / 8;            // 16-byte chunks per row
   constexpr int TILE_BYTES = BN * DH * 2;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -141,15 +142,15 @@ multi_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache, T 
   bool const anybit = s_anybit != 0;
   int const rA = warp * 16 + (lane >> 2), rB = rA + 8;
   int const tq = lane & 3;
-  if (k0 >= kv_hi) {
-    if (nsplit == 1) { // no keys at all: zero output rows
-      for (int i = tid; i < BM * (DH / 2); i += MQ_THREADS) {
-        int r = i / (DH / 2), c = i % (DH / 2);
-        if (s_tok[r] >= 0) {
-          reinterpret_cast<uint32_t *>(out + (size_t)s_tok[r] * DH)[c] = 0u;
-        }
+  if (split == 0 && kv_lo <= 0) { // rows without any key: zero output (no split will touch them)
+    for (int i = tid; i < BM * (DH / 2); i += MQ_THREADS) {
+      int r = i / (DH / 2), c = i % (DH / 2);
+      if (s_tok[r] >= 0 && s_kvlen[r] <= 0) {
+        reinterpret_cast<uint32_t *>(out + (size_t)s_tok[r] * DH)[c] = 0u;
       }
     }
+  }
+  if (k0 >= kv_hi) {
     return;
   }
   int const k1 = min(k0 + chunk, kv_hi);
@@ -334,6 +335,34 @@ multi_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache, T 
         rec[DH + 1] = lB;
       }
     }
+    if (fuse_combine) {
+      // per-row arrival counters: the last split to finish a (token, head) row merges its records
+      __shared__ int s_rowlast[BM];
+      __threadfence();
+      __syncthreads();
+      if (tid < BM) {
+        int const th = s_tok[tid];
+        int last = 0;
+        if (th >= 0 && k0 < s_kvlen[tid]) {
+          int const nvalid = min(nsplit, (s_kvlen[tid] + chunk - 1) / chunk);
+          int const prev = atomicAdd(&split_counter[th], 1);
+          last = prev == nvalid - 1;
+          if (last) {
+            split_counter[th] = 0;
+          }
+        }
+        s_rowlast[tid] = last;
+      }
+      __syncthreads();
+      __threadfence();
+      for (int r = warp; r < BM; r += MQ_THREADS / 32) {
+        if (s_rowlast[r]) {
+          int const th = s_tok[r];
+          int const nvalid = min(nsplit, (s_kvlen[r] + chunk - 1) / chunk);
+          combine_record<T, DH>(partial + (size_t)th * nsplit * (DH + 2), nvalid, out + (size_t)th * DH, lane, 32);
+        }
+      }
+    }
   }
 }
 
@@ -359,6 +388,7 @@ int launch_multi_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta,
   }
   float const scale = d.qk_prod_scaling ? 1.0f / sqrtf((float)d.head_dim) : 1.0f;
   float const scale_log2 = scale * 1.4426950408889634f;
+  int const fuse = getenv("FFB_SEPARATE_COMBINE") ? 0 : 1;
   dim3 grid(nsplit, d.num_kv_heads * m_tiles, d.max_requests);
   if (h->profiling) {
     cudaEventRecord(h->ev0, s);
@@ -373,8 +403,8 @@ int launch_multi_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta,
     }                                                                                                      \
     multi_attn_kernel<TT, DH><<<grid, MQ_THREADS, smem, s>>>(                                              \
         (TT const *)h->q_buf, (TT const *)h->k_cache, (TT const *)h->v_cache, h->qdesc, meta, h->partial,  \
-        (TT *)out, d.mode, d.num_q_heads, d.num_kv_heads, h->cache_len, m_tiles, chunk, nsplit, scale_log2, \
-        h->num_generation_tokens_cur);                                                                     \
+        h->split_counter, (TT *)out, d.mode, d.num_q_heads, d.num_kv_heads, h->cache_len, m_tiles, chunk, nsplit, \
+        scale_log2, h->num_generation_tokens_cur, fuse);                                                                     \
   } while (0)
   if (d.dtype == FFB_DT_HALF) {
     if (d.head_dim == 128) FFB_MQ(__half, 128); else FFB_MQ(__half, 64);
@@ -386,7 +416,7 @@ int launch_multi_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta,
     cudaEventRecord(h->ev1, s);
   }
   FFB_LAUNCH_CHECK();
-  if (nsplit > 1) {
+  if (nsplit > 1 && !fuse) {
     return launch_combine(h, out, T, chunk, nsplit, s);
   }
   return FFB_OK;

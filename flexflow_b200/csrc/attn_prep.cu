@@ -72,7 +72,7 @@ prep_kernel(T const *__restrict__ qkv, T *__restrict__ q_buf, T *__restrict__ k_
     }
   }
   bool const pos_ok = slot_ok && cache_pos >= 0 && cache_pos < cache_len;
-  if (threadIdx.x == 0) {
+  if (threadIdx.x == 0 && blockIdx.y == 0) {
     QueryDesc qd;
     qd.slot = slot_ok ? slot : 0;
     qd.kv_len = slot_ok ? max(0, min(kv_len, cache_len)) : 0;
@@ -112,57 +112,60 @@ prep_kernel(T const *__restrict__ qkv, T *__restrict__ q_buf, T *__restrict__ k_
   constexpr int CH = DH / 16; // 16-byte chunks per half head
   T const *row = qkv + (size_t)t * 3 * H;
   // rotate Q heads (-> q_buf) and the distinct K heads (-> cache, prev_kv)
+  // work items of this token (rotate-Q/K chunks, then V chunks) are spread over gridDim.y blocks
   int const n_rot = (nq + nkv) * CH;
-  for (int w = threadIdx.x; w < n_rot; w += blockDim.x) {
-    int const head = w / CH, c = w % CH;
-    bool const is_q = head < nq;
-    int const src_head = is_q ? head : (head - nq) * G;
-    T const *src = row + (is_q ? 0 : H) + src_head * DH + c * 8;
-    uint4 ux = *reinterpret_cast<uint4 const *>(src);
-    uint4 uy = *reinterpret_cast<uint4 const *>(src + DH / 2);
-    float x[8], y[8], ox[8], oy[8];
-    unpack8<T>(ux, x);
-    unpack8<T>(uy, y);
+  int const n_v = nkv * (DH / 8);
+  int const tstride = blockDim.x * gridDim.y;
+  for (int item = blockIdx.y * blockDim.x + threadIdx.x; item < n_rot + n_v; item += tstride) {
+    if (item < n_rot) {
+      int const head = item / CH, c = item % CH;
+      bool const is_q = head < nq;
+      int const src_head = is_q ? head : (head - nq) * G;
+      T const *src = row + (is_q ? 0 : H) + src_head * DH + c * 8;
+      uint4 ux = *reinterpret_cast<uint4 const *>(src);
+      uint4 uy = *reinterpret_cast<uint4 const *>(src + DH / 2);
+      float x[8], y[8], ox[8], oy[8];
+      unpack8<T>(ux, x);
+      unpack8<T>(uy, y);
 #pragma unroll
-    for (int e = 0; e < 8; e++) {
-      float xv = x[e], yv = y[e];
-      if (is_q && scaling_query) { // scaling_query_kernel stores DT (inc_…cu:650-662)
-        xv = DT<T>::to_f(DT<T>::from_f(xv * scaling_factor));
-        yv = DT<T>::to_f(DT<T>::from_f(yv * scaling_factor));
+      for (int e = 0; e < 8; e++) {
+        float xv = x[e], yv = y[e];
+        if (is_q && scaling_query) { // scaling_query_kernel stores DT (inc_…cu:650-662)
+          xv = DT<T>::to_f(DT<T>::from_f(xv * scaling_factor));
+          yv = DT<T>::to_f(DT<T>::from_f(yv * scaling_factor));
+        }
+        float cs = s_cos[c * 8 + e], sn = s_sin[c * 8 + e];
+        ox[e] = xv * cs - yv * sn; // cuCmulf
+        oy[e] = xv * sn + yv * cs;
       }
-      float cs = s_cos[c * 8 + e], sn = s_sin[c * 8 + e];
-      ox[e] = xv * cs - yv * sn; // cuCmulf
-      oy[e] = xv * sn + yv * cs;
-    }
-    uint4 px = pack8<T>(ox), py = pack8<T>(oy);
-    if (is_q) {
-      T *dst = q_buf + ((size_t)t * nq + head) * DH + c * 8;
-      *reinterpret_cast<uint4 *>(dst) = px;
-      *reinterpret_cast<uint4 *>(dst + DH / 2) = py;
-    } else {
-      int const j = head - nq;
-      if (pos_ok) {
-        T *dst = k_cache + (((size_t)slot * nkv + j) * cache_len + cache_pos) * DH + c * 8;
+      uint4 px = pack8<T>(ox), py = pack8<T>(oy);
+      if (is_q) {
+        T *dst = q_buf + ((size_t)t * nq + head) * DH + c * 8;
         *reinterpret_cast<uint4 *>(dst) = px;
         *reinterpret_cast<uint4 *>(dst + DH / 2) = py;
+      } else {
+        int const j = head - nq;
+        if (pos_ok) {
+          T *dst = k_cache + (((size_t)slot * nkv + j) * cache_len + cache_pos) * DH + c * 8;
+          *reinterpret_cast<uint4 *>(dst) = px;
+          *reinterpret_cast<uint4 *>(dst + DH / 2) = py;
+        }
+        if (prev_kv) {
+          T *dst = prev_kv + (((size_t)t * 2 + 0) * nkv + j) * DH + c * 8;
+          *reinterpret_cast<uint4 *>(dst) = px;
+          *reinterpret_cast<uint4 *>(dst + DH / 2) = py;
+        }
+      }
+    } else { // V heads: straight copy
+      int const w = item - n_rot;
+      int const j = w / (DH / 8), c = w % (DH / 8);
+      uint4 u = *reinterpret_cast<uint4 const *>(row + 2 * H + j * G * DH + c * 8);
+      if (pos_ok) {
+        *reinterpret_cast<uint4 *>(v_cache + (((size_t)slot * nkv + j) * cache_len + cache_pos) * DH + c * 8) = u;
       }
       if (prev_kv) {
-        T *dst = prev_kv + (((size_t)t * 2 + 0) * nkv + j) * DH + c * 8;
-        *reinterpret_cast<uint4 *>(dst) = px;
-        *reinterpret_cast<uint4 *>(dst + DH / 2) = py;
+        *reinterpret_cast<uint4 *>(prev_kv + (((size_t)t * 2 + 1) * nkv + j) * DH + c * 8) = u;
       }
-    }
-  }
-  // V heads: straight copy
-  int const n_v = nkv * (DH / 8);
-  for (int w = threadIdx.x; w < n_v; w += blockDim.x) {
-    int const j = w / (DH / 8), c = w % (DH / 8);
-    uint4 u = *reinterpret_cast<uint4 const *>(row + 2 * H + j * G * DH + c * 8);
-    if (pos_ok) {
-      *reinterpret_cast<uint4 *>(v_cache + (((size_t)slot * nkv + j) * cache_len + cache_pos) * DH + c * 8) = u;
-    }
-    if (prev_kv) {
-      *reinterpret_cast<uint4 *>(prev_kv + (((size_t)t * 2 + 1) * nkv + j) * DH + c * 8) = u;
     }
   }
 }
@@ -214,8 +217,14 @@ static int launch_prep_t(ffb_attn_s *h, int mode, ffb_combined_batch_config_meta
   RopeParams rp{d.apply_rotary_embedding, d.rope_theta, d.rope_llama3, d.rope_factor,
                 d.rope_low_freq_factor, d.rope_high_freq_factor, d.rope_original_max_position_embeddings};
   T *prev = mode == FFB_TREE_VERIFY_MODE ? (T *)h->prev_kv : nullptr;
+  // enough blocks to cover ~2 waves of SMs, at most one item per thread
+  int const items = (d.num_q_heads + d.num_kv_heads) * (d.head_dim / 16) + d.num_kv_heads * (d.head_dim / 8);
+  int pb = (items + 127) / 128;
+  while (pb > 1 && (long)T_ * pb > 4L * kNumSMs) {
+    pb = (pb + 1) / 2;
+  }
 #define FFB_PREP(DH)                                                                                   \
-  prep_kernel<T, DH><<<T_, 128, 0, s>>>((T const *)qkv, (T *)h->q_buf, (T *)h->k_cache, (T *)h->v_cache, \
+  prep_kernel<T, DH><<<dim3(T_, pb), 128, 0, s>>>((T const *)qkv, (T *)h->q_buf, (T *)h->k_cache, (T *)h->v_cache, \
                                         prev, h->qdesc, meta, mode, d.num_q_heads, d.num_kv_heads,     \
                                         h->cache_len, d.max_requests, rp, d.scaling_query,             \
                                         d.scaling_factor, ngen)

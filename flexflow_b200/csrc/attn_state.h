@@ -17,6 +17,7 @@ struct ffb_attn_s {
   void *q_buf = nullptr;   // rotated queries [max_tokens][num_q_heads][head_dim]
   void *prev_kv = nullptr; // K,V of the previous batch [max_tokens][2][num_kv_heads][head_dim] (commit source)
   ffb::QueryDesc *qdesc = nullptr; // [max_tokens]
+  int *split_counter = nullptr;    // [max_tokens*num_q_heads] arrival counters (self-resetting) for the fused combine
   float *partial = nullptr;        // split-KV partials
   size_t partial_bytes = 0;
   // m->profiling (inc_…cu:1510-1538): events around the dominant attention kernel only

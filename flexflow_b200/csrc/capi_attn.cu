@@ -78,6 +78,7 @@ int ffb_attn_create(ffb_attn_desc const *desc, ffb_attn_t *out) {
   size_t const prev_b = d.mode == FFB_TREE_VERIFY_MODE
                             ? align((size_t)d.max_tokens_per_batch * 2 * d.num_kv_heads * d.head_dim * h->elt) : 0;
   size_t const qd_b = align((size_t)d.max_tokens_per_batch * sizeof(QueryDesc));
+  size_t const cnt_b = align((size_t)d.max_tokens_per_batch * d.num_q_heads * sizeof(int));
   size_t const rec = (size_t)(d.head_dim + 2) * sizeof(float);
   size_t part = (size_t)d.max_tokens_per_batch * d.num_q_heads * 8 * rec;
   size_t const part_min = (size_t)d.num_q_heads * ((h->cache_len + 63) / 64) * rec * 2;
@@ -88,7 +89,7 @@ int ffb_attn_create(ffb_attn_desc const *desc, ffb_attn_t *out) {
     part = part_min;
   }
   h->partial_bytes = align(part);
-  h->bytes = 2 * cache_b + q_b + prev_b + qd_b + h->partial_bytes;
+  h->bytes = 2 * cache_b + q_b + prev_b + qd_b + cnt_b + h->partial_bytes;
   cudaError_t e = cudaMalloc(&h->base, h->bytes);
   if (e != cudaSuccess) {
     set_error("cudaMalloc(%zu bytes) failed: %s", h->bytes, cudaGetErrorString(e));
@@ -101,6 +102,7 @@ int ffb_attn_create(ffb_attn_desc const *desc, ffb_attn_t *out) {
   h->q_buf = p; p += q_b;
   h->prev_kv = prev_b ? p : nullptr; p += prev_b;
   h->qdesc = (QueryDesc *)p; p += qd_b;
+  h->split_counter = (int *)p; p += cnt_b;
   h->partial = (float *)p;
   e = cudaMemset(h->base, 0, h->bytes);
   if (e != cudaSuccess) {

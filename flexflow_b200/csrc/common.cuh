@@ -98,6 +98,50 @@ struct QueryDesc {
   int bit;
 };
 
+__device__ __forceinline__ float ffb_ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// Exact log-sum-exp merge of the split-KV partial records of one (token, head) followed by the
+// reference's 1/(sum + 1e-6) normalisation (inc_…cu:538).  Called by `nthreads` threads with ids
+// [0, nthreads); each thread produces elements tid, tid+nthreads, ...  Records are read with ld.cg
+// (written by other blocks of the same launch).
+template <typename T, int DH>
+__device__ __forceinline__ void combine_record(float const *rec, int nvalid, T *out_row, int tid, int nthreads) {
+  float M = -INFINITY;
+  for (int i = 0; i < nvalid; i++) {
+    M = fmaxf(M, __ldcg(rec + i * (DH + 2) + DH));
+  }
+  float L = 0.f;
+  float o[(DH + 31) / 32];
+#pragma unroll
+  for (int j = 0; j < (DH + 31) / 32; j++) {
+    o[j] = 0.f;
+  }
+  for (int i = 0; i < nvalid; i++) {
+    float const mi = __ldcg(rec + i * (DH + 2) + DH);
+    float const w = (mi == -INFINITY) ? 0.f : ffb_ex2(mi - M);
+    L += __ldcg(rec + i * (DH + 2) + DH + 1) * w;
+#pragma unroll
+    for (int j = 0; j < (DH + 31) / 32; j++) {
+      int const d = tid + j * nthreads;
+      if (d < DH) {
+        o[j] += __ldcg(rec + i * (DH + 2) + d) * w;
+      }
+    }
+  }
+  float const inv = __fdividef(1.f, L + 1.e-6f);
+#pragma unroll
+  for (int j = 0; j < (DH + 31) / 32; j++) {
+    int const d = tid + j * nthreads;
+    if (d < DH) {
+      out_row[d] = DT<T>::from_f(o[j] * inv);
+    }
+  }
+}
+
 struct RopeParams {
   int apply;
   float theta;

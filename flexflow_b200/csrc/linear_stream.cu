@@ -9,6 +9,8 @@
 // A block owns NT*8 consecutive output features (inside one 32-row quantisation group, so all its
 // warps share scale/offset columns); its 8 warps split K in interleaved chunks and are summed in a
 // fixed order through shared memory (deterministic).
+#include <cstdlib>
+
 #include "dequant.cuh"
 
 namespace ffb {
@@ -20,14 +22,14 @@ __device__ __forceinline__ void mma16816(float (&c)[4], uint32_t a0, uint32_t a1
 template <>
 __device__ __forceinline__ void mma16816<__half>(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2,
                                                  uint32_t a3, uint32_t b0, uint32_t b1) {
-  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+  asm("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
                : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 template <>
 __device__ __forceinline__ void mma16816<__nv_bfloat16>(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2,
                                                         uint32_t a3, uint32_t b0, uint32_t b1) {
-  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+  asm("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
                : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
@@ -45,7 +47,7 @@ constexpr int LS_WARPS = 8;
 // permutation applied identically to A and B (a dot product is order-free), chosen so every lane
 // reads 16 contiguous bytes of a weight row.
 template <typename T, int QB, int NT, int MT>
-__global__ void __launch_bounds__(LS_WARPS * 32)
+__global__ void __launch_bounds__(LS_WARPS * 32, MT == 1 ? 2 : 1)
 linear_stream_kernel(T const *__restrict__ A, uint8_t const *__restrict__ W, T const *__restrict__ bias,
                      T *__restrict__ out, int M, int K, int N) {
   constexpr int KE = QB == 0 ? 8 : (QB == 8 ? 16 : 32); // k elements per lane per chunk (16 B of weights)
@@ -72,94 +74,130 @@ linear_stream_kernel(T const *__restrict__ A, uint8_t const *__restrict__ W, T c
   }
 
   int const nchunks = K / KC;
-#pragma unroll 2
-  for (int kc = warp; kc < nchunks; kc += LS_WARPS) {
-    int const k = kc * KC + tq * KE;
-    uint4 w[NT];
+  // U chunks per warp are fetched back-to-back BEFORE any of them is consumed, so U*(NT + 2*MT*AP [+ 2*AP])
+  // 16-byte loads are in flight per lane: at M <= 16 the kernel is a pure weight stream and its speed is
+  // set by bytes in flight, not by the MMAs.
+  constexpr int U = MT == 1 ? (QB == 0 ? 4 : (QB == 8 ? 2 : 1)) : ((MT == 2 && QB == 0) ? 2 : 1);
+  constexpr int QP = QB == 0 ? 1 : AP;
+  for (int kc0 = warp; kc0 < nchunks; kc0 += LS_WARPS * U) {
+    uint4 w[U][NT], sc[U][QP], of[U][QP], alo[U][MT][AP], ahi[U][MT][AP];
 #pragma unroll
-    for (int nt = 0; nt < NT; nt++) {
-      size_t const e = (size_t)(n0 + nt * 8 + g) * K + k;
-      w[nt] = ldg_stream(QB == 0 ? W + e * 2 : (QB == 8 ? W + e : W + e / 2));
-    }
-    uint4 sc[QB == 0 ? 1 : AP], of[QB == 0 ? 1 : AP];
-    if (QB != 0) {
-#pragma unroll
-      for (int p = 0; p < AP; p++) {
-        sc[p] = *reinterpret_cast<uint4 const *>(scales + meta_row + k + p * 8);
-        of[p] = *reinterpret_cast<uint4 const *>(offs + meta_row + k + p * 8);
-      }
-    }
-    uint4 alo[MT][AP], ahi[MT][AP];
-#pragma unroll
-    for (int mt = 0; mt < MT; mt++) {
-      int const r0 = mt * 16 + g, r1 = r0 + 8;
-#pragma unroll
-      for (int p = 0; p < AP; p++) {
-        alo[mt][p] = r0 < M ? *reinterpret_cast<uint4 const *>(A + (size_t)r0 * K + k + p * 8) : make_uint4(0, 0, 0, 0);
-        ahi[mt][p] = r1 < M ? *reinterpret_cast<uint4 const *>(A + (size_t)r1 * K + k + p * 8) : make_uint4(0, 0, 0, 0);
-      }
-    }
-#pragma unroll
-    for (int s = 0; s < STEPS; s++) {
-      int const p = (4 * s) / 8, wi = ((4 * s) % 8) / 2; // activation piece / 32-bit word of elements 4s..4s+3
-      uint32_t b0[NT], b1[NT];
-      if (QB == 0) {
+    for (int u = 0; u < U; u++) {
+      int const kc = kc0 + u * LS_WARPS;
+      if (kc < nchunks) {
+        int const k = kc * KC + tq * KE;
 #pragma unroll
         for (int nt = 0; nt < NT; nt++) {
-          b0[nt] = word(w[nt], 2 * s);
-          b1[nt] = word(w[nt], 2 * s + 1);
+          size_t const e = (size_t)(n0 + nt * 8 + g) * K + k;
+          w[u][nt] = ldg_stream(QB == 0 ? W + e * 2 : (QB == 8 ? W + e : W + e / 2));
         }
-      } else {
-        typename DqCoef<T>::type cf[4];
-        T const *ps = reinterpret_cast<T const *>(&sc[p]);
-        T const *po = reinterpret_cast<T const *>(&of[p]);
+        if (QB != 0) {
 #pragma unroll
-        for (int e = 0; e < 4; e++) {
-          cf[e] = dq_coef(ps[(4 * s) % 8 + e], po[(4 * s) % 8 + e]);
-        }
-#pragma unroll
-        for (int nt = 0; nt < NT; nt++) {
-          int q0, q1, q2, q3;
-          if (QB == 8) {
-            uint32_t const v = word(w[nt], s);
-            q0 = v & 0xFF; q1 = (v >> 8) & 0xFF; q2 = (v >> 16) & 0xFF; q3 = v >> 24;
-          } else {
-            uint32_t const v = (word(w[nt], s / 2) >> (16 * (s & 1))) & 0xFFFFu;
-            q0 = (v >> 4) & 0xF; q1 = v & 0xF; q2 = (v >> 12) & 0xF; q3 = (v >> 8) & 0xF;
+          for (int p = 0; p < QP; p++) {
+            sc[u][p] = __ldg(reinterpret_cast<uint4 const *>(scales + meta_row + k + p * 8));
+            of[u][p] = __ldg(reinterpret_cast<uint4 const *>(offs + meta_row + k + p * 8));
           }
-          b0[nt] = pack2<T>(dq_elem(q0, cf[0]), dq_elem(q1, cf[1]));
-          b1[nt] = pack2<T>(dq_elem(q2, cf[2]), dq_elem(q3, cf[3]));
+        }
+#pragma unroll
+        for (int mt = 0; mt < MT; mt++) {
+          int const r0 = mt * 16 + g, r1 = r0 + 8;
+#pragma unroll
+          for (int p = 0; p < AP; p++) {
+            alo[u][mt][p] = r0 < M ? __ldg(reinterpret_cast<uint4 const *>(A + (size_t)r0 * K + k + p * 8)) : make_uint4(0, 0, 0, 0);
+            ahi[u][mt][p] = r1 < M ? __ldg(reinterpret_cast<uint4 const *>(A + (size_t)r1 * K + k + p * 8)) : make_uint4(0, 0, 0, 0);
+          }
         }
       }
+    }
 #pragma unroll
-      for (int mt = 0; mt < MT; mt++) {
-        uint32_t const a0 = word(alo[mt][p], wi), a2 = word(alo[mt][p], wi + 1);
-        uint32_t const a1 = word(ahi[mt][p], wi), a3 = word(ahi[mt][p], wi + 1);
+    for (int u = 0; u < U; u++) {
+      if (kc0 + u * LS_WARPS < nchunks) {
 #pragma unroll
-        for (int nt = 0; nt < NT; nt++) {
-          mma16816<T>(acc[mt][nt], a0, a1, a2, a3, b0[nt], b1[nt]);
+        for (int s = 0; s < STEPS; s++) {
+          int const p = (4 * s) / 8, wi = ((4 * s) % 8) / 2; // activation piece / 32-bit word of elements 4s..4s+3
+          uint32_t b0[NT], b1[NT];
+          if (QB == 0) {
+#pragma unroll
+            for (int nt = 0; nt < NT; nt++) {
+              b0[nt] = word(w[u][nt], 2 * s);
+              b1[nt] = word(w[u][nt], 2 * s + 1);
+            }
+          } else {
+            typename DqCoef<T>::type cf[4];
+            T const *ps = reinterpret_cast<T const *>(&sc[u][QB == 0 ? 0 : p]);
+            T const *po = reinterpret_cast<T const *>(&of[u][QB == 0 ? 0 : p]);
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+              cf[e] = dq_coef(ps[(4 * s) % 8 + e], po[(4 * s) % 8 + e]);
+            }
+#pragma unroll
+            for (int nt = 0; nt < NT; nt++) {
+              int q0, q1, q2, q3;
+              if (QB == 8) {
+                uint32_t const v = word(w[u][nt], s);
+                q0 = v & 0xFF; q1 = (v >> 8) & 0xFF; q2 = (v >> 16) & 0xFF; q3 = v >> 24;
+              } else {
+                uint32_t const v = (word(w[u][nt], s / 2) >> (16 * (s & 1))) & 0xFFFFu;
+                q0 = (v >> 4) & 0xF; q1 = v & 0xF; q2 = (v >> 12) & 0xF; q3 = (v >> 8) & 0xF;
+              }
+              b0[nt] = pack2<T>(dq_elem(q0, cf[0]), dq_elem(q1, cf[1]));
+              b1[nt] = pack2<T>(dq_elem(q2, cf[2]), dq_elem(q3, cf[3]));
+            }
+          }
+#pragma unroll
+          for (int mt = 0; mt < MT; mt++) {
+            uint32_t const a0 = word(alo[u][mt][p], wi), a2 = word(alo[u][mt][p], wi + 1);
+            uint32_t const a1 = word(ahi[u][mt][p], wi), a3 = word(ahi[u][mt][p], wi + 1);
+#pragma unroll
+            for (int nt = 0; nt < NT; nt++) {
+              mma16816<T>(acc[mt][nt], a0, a1, a2, a3, b0[nt], b1[nt]);
+            }
+          }
         }
       }
     }
   }
 
-  // fixed-order sum over the 8 k-slices
+  // fixed-order (deterministic) sum over the 8 k-slices
   __shared__ float tile[MT * 16][NT * 8 + 1];
-  for (int wsel = 0; wsel < LS_WARPS; wsel++) {
-    if (warp == wsel) {
+  if constexpr (MT == 1) {
+    // every warp parks its fragment, then each output is summed over the warps in index order
+    __shared__ float red[LS_WARPS][16][NT * 8 + 1];
 #pragma unroll
-      for (int mt = 0; mt < MT; mt++) {
+    for (int nt = 0; nt < NT; nt++) {
 #pragma unroll
-        for (int nt = 0; nt < NT; nt++) {
-#pragma unroll
-          for (int e = 0; e < 4; e++) {
-            int const r = mt * 16 + g + (e >> 1) * 8, c = nt * 8 + 2 * tq + (e & 1);
-            tile[r][c] = wsel == 0 ? acc[mt][nt][e] : tile[r][c] + acc[mt][nt][e];
-          }
-        }
+      for (int e = 0; e < 4; e++) {
+        red[warp][g + (e >> 1) * 8][nt * 8 + 2 * tq + (e & 1)] = acc[0][nt][e];
       }
     }
     __syncthreads();
+    for (int i = tid; i < 16 * NT * 8; i += LS_WARPS * 32) {
+      int const r = i / (NT * 8), c = i % (NT * 8);
+      float v = 0.f;
+#pragma unroll
+      for (int w = 0; w < LS_WARPS; w++) {
+        v += red[w][r][c];
+      }
+      tile[r][c] = v;
+    }
+    __syncthreads();
+  } else {
+    for (int wsel = 0; wsel < LS_WARPS; wsel++) {
+      if (warp == wsel) {
+#pragma unroll
+        for (int mt = 0; mt < MT; mt++) {
+#pragma unroll
+          for (int nt = 0; nt < NT; nt++) {
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+              int const r = mt * 16 + g + (e >> 1) * 8, c = nt * 8 + 2 * tq + (e & 1);
+              tile[r][c] = wsel == 0 ? acc[mt][nt][e] : tile[r][c] + acc[mt][nt][e];
+            }
+          }
+        }
+      }
+      __syncthreads();
+    }
   }
   constexpr int SEGS = NT; // 8-column (16 B) segments per row
   if (tid < MT * 16 * SEGS) {
@@ -187,7 +225,10 @@ int launch_linear_stream(int dtype, int quant, void const *in, void *out, void c
   FFB_REQUIRE(K % KC == 0 && N % 32 == 0, "linear_stream needs in_dim %% %d == 0 and out_dim %% 32 == 0", KC);
   FFB_REQUIRE(M >= 1 && M <= 64, "linear_stream handles 1..64 rows, got %d", M);
   int const MT = M <= 16 ? 1 : (M <= 32 ? 2 : 4);
-  int const NT = (N / 32 >= 2 * kNumSMs) ? 4 : 2;
+  int NT = (N / 32 >= 2 * kNumSMs) ? 4 : 2;
+  if (char const *e = getenv("FFB_LS_NT")) {
+    NT = atoi(e) == 4 ? 4 : 2;
+  }
   dim3 grid(N / (NT * 8));
 #define FFB_LS(TT, QB, NTv, MTv)                                                                             \
   linear_stream_kernel<TT, QB, NTv, MTv><<<grid, LS_WARPS * 32, 0, s>>>((TT const *)in, (uint8_t const *)w, \

@@ -1,0 +1,97 @@
+"""Attention-operator micro-benchmark at the BASELINE.json shapes: kernel time (CUDA events around the
+dominant kernel, via ffb_attn_set_profiling) and algorithmic HBM GB/s (SURVEY §8d bytes).
+    python tools/bench_attn.py [--json out.json]"""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import ffb_testlib as TL  # noqa: E402
+from flexflow_b200 import batch_config as B  # noqa: E402
+from flexflow_b200 import ops  # noqa: E402
+
+PEAK = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+
+
+def run(name, mode, nq, nkv, dh, reqs_fn, max_req, max_seq, max_tok, layers=6, iters=10):
+    h = ops.FFHandler("cuda:0")
+    cls = {B.INC_DECODING_MODE: (ops.IncMultiHeadSelfAttentionMeta, ops.IncMultiHeadSelfAttention),
+           B.TREE_VERIFY_MODE: (ops.TreeIncMultiHeadSelfAttentionMeta, ops.TreeIncMultiHeadSelfAttention)}[mode]
+    rope = ops.RotaryEmbeddingMeta(apply_rotary_embedding=True)
+    metas = [cls[0](h, nq, nkv, dh, rotary_embedding_meta=rope, max_requests_per_batch=max_req,
+                    max_tokens_per_batch=max_tok, max_sequence_length=max_seq) for _ in range(layers)]
+    bc, lens = reqs_fn()
+    g = torch.Generator(device="cuda").manual_seed(0)
+    for m in metas:  # several "layers" so the KV working set exceeds the 126 MB L2
+        for s, n in lens.items():
+            kv = torch.randn(n, nkv, dh, generator=g, device="cuda", dtype=torch.float16)
+            m.write_kv(s, 0, kv, kv)
+        m.set_profiling(True)
+    T = bc.num_tokens
+    qkv = torch.randn(T, 3, nq * dh, generator=g, device="cuda", dtype=torch.float16)
+    out = torch.empty(T, nq * dh, device="cuda", dtype=torch.float16)
+    h.load_batch_config(bc)
+    kms, tot = [], []
+    for it in range(iters + 2):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for m in metas:
+            if mode == B.TREE_VERIFY_MODE:
+                bc.num_tokens_to_commit = 0
+            cls[1].inference_kernel_wrapper(m, bc, 0, qkv, out)
+        e1.record()
+        torch.cuda.synchronize()
+        if it >= 2:
+            kms.extend(m.last_kernel_ms() for m in metas)
+            tot.append(e0.elapsed_time(e1) / layers)
+    elt = 2
+    kv_bytes = 2 * sum(lens[s] + (bc.requestsInfo[s].num_tokens_in_batch) for s in lens) * nkv * dh * elt
+    alg = kv_bytes + T * (nq + 2 * nkv) * dh * elt + T * nq * dh * elt + 2 * T * nkv * dh * elt
+    k_ms = float(np.mean(kms))
+    r = dict(case=name, tokens=T, kernel_ms=k_ms, op_ms=float(np.mean(tot)), algorithmic_mb=alg / 1e6,
+             gbs=alg / k_ms / 1e6, frac_of_measured_peak=alg / k_ms / 1e6 / PEAK)
+    print(r, flush=True)
+    for m in metas:
+        m.close()
+    return r
+
+
+def main():
+    rng = np.random.default_rng(0)
+    res = []
+    only = sys.argv[sys.argv.index("--only") + 1] if "--only" in sys.argv else None
+
+    def decode7b():
+        lens = {s: 2047 for s in range(16)}
+        return TL.make_inc_batch([dict(slot=s, first_depth=2047, ntok=1) for s in range(16)]), lens
+    res.append(run("cfg2 7B decode b16 ctx2048", B.INC_DECODING_MODE, 32, 32, 128, decode7b, 16, 2048, 16))
+    if only == "cfg2":
+        return
+
+    def tree7b(ntree):
+        def f():
+            lens = {s: 1024 for s in range(8)}
+            return TL.make_tree_batch([dict(slot=s, committed_len=1024, parent=TL.random_tree(rng, ntree)) for s in range(8)]), lens
+        return f
+    res.append(run("cfg4 7B tree-verify b8 x64 ctx1024", B.TREE_VERIFY_MODE, 32, 32, 128, tree7b(64), 8, 1100, 512))
+    res.append(run("cfg4' 7B tree-verify b8 x25 ctx1024 (reference max tree)", B.TREE_VERIFY_MODE, 32, 32, 128, tree7b(25), 8, 1100, 512))
+
+    def tree70b():
+        lens = {s: 4096 for s in range(32)}
+        return TL.make_tree_batch([dict(slot=s, committed_len=4096, parent=TL.random_tree(rng, 32)) for s in range(32)]), lens
+    res.append(run("cfg5 70B tree-verify b32 x32 ctx4096, TP=8 shard (8q/1kv)", B.TREE_VERIFY_MODE, 8, 1, 128, tree70b, 32, 4200, 1024, layers=8))
+
+    def prompt7b():
+        return TL.make_inc_batch([dict(slot=0, first_depth=0, ntok=1024, prompt=True)]), {0: 0}
+    res.append(run("7B prefill 1x1024", B.INC_DECODING_MODE, 32, 32, 128, prompt7b, 2, 2048, 1024, layers=2))
+    if "--json" in sys.argv:
+        json.dump(res, open(sys.argv[sys.argv.index("--json") + 1], "w"), indent=1)
+
+
+if __name__ == "__main__":
+    main()
