@@ -18,6 +18,7 @@ SOURCES = [
     "capi_attn.cu",
     "dequant.cu",
     "linear_stream.cu",
+    "linear_gemv.cu",
     "linear_tc.cu",
     "capi_linear.cu",
     "comm.cu",

@@ -18,7 +18,7 @@ int choose_chunk(ffb_attn_s *h, long units, int kv_len_max, int granule, long ta
 
 namespace {
 
-constexpr int BM = 64, BN = 64, MQ_THREADS = 128;
+constexpr int BM = 64, BN = 64, MQ_THREADS = 256; // 8 warps = 4 row groups (16 query rows) x 2 key halves (32 keys)
 
 __device__ __forceinline__ float ex2(float x) {
   float y;
@@ -106,6 +106,7 @@ multi_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache, T 
   }
   int const split = blockIdx.x, k0 = split * chunk;
   int const tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  int const rg = warp & 3, kh = warp >> 2; // row group, key half of every 64-key tile
   int const ntcs = meta->causalMask[slot].non_tree_cache_size;
 
   if (tid == 0) {
@@ -140,7 +141,7 @@ multi_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache, T 
   __syncthreads();
   int const kv_hi = s_hi, kv_lo = s_lo;
   bool const anybit = s_anybit != 0;
-  int const rA = warp * 16 + (lane >> 2), rB = rA + 8;
+  int const rA = rg * 16 + (lane >> 2), rB = rA + 8;
   int const tq = lane & 3;
   if (split == 0 && kv_lo <= 0) { // rows without any key: zero output (no split will touch them)
     for (int i = tid; i < BM * (DH / 2); i += MQ_THREADS) {
@@ -204,20 +205,20 @@ multi_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache, T 
     int const kt = k0 + it * BN;
     uint32_t const sKb = sKa + buf * TILE_BYTES, sVb = sVa + buf * TILE_BYTES;
 
-    // S = Q K^T  (16 rows x 64 keys per warp)
-    float s[8][4];
+    // S = Q K^T  (16 rows x 32 keys per warp)
+    float s[4][4];
 #pragma unroll
-    for (int j = 0; j < 8; j++) {
+    for (int j = 0; j < 4; j++) {
       s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
     }
 #pragma unroll
     for (int ks = 0; ks < DH / 16; ks++) {
       uint32_t a0, a1, a2, a3;
-      ldsm_x4(sQa + swz<DH>(warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, ks * 2 + (lane >> 4)), a0, a1, a2, a3);
+      ldsm_x4(sQa + swz<DH>(rg * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, ks * 2 + (lane >> 4)), a0, a1, a2, a3);
 #pragma unroll
-      for (int np = 0; np < 4; np++) {
+      for (int np = 0; np < 2; np++) {
         uint32_t b0, b1, b2, b3;
-        ldsm_x4(sKb + swz<DH>(np * 16 + (lane & 7) + (lane >> 4) * 8, ks * 2 + ((lane >> 3) & 1)), b0, b1, b2, b3);
+        ldsm_x4(sKb + swz<DH>(kh * 32 + np * 16 + (lane & 7) + (lane >> 4) * 8, ks * 2 + ((lane >> 3) & 1)), b0, b1, b2, b3);
         mma16816<T>(s[2 * np], a0, a1, a2, a3, b0, b1);
         mma16816<T>(s[2 * np + 1], a0, a1, a2, a3, b2, b3);
       }
@@ -226,12 +227,12 @@ multi_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache, T 
     bool const need_mask = (kt + BN > kv_lo) || (kt + BN > k1) || (anybit && kt + BN > ntcs);
     float mxA = -INFINITY, mxB = -INFINITY;
 #pragma unroll
-    for (int j = 0; j < 8; j++) {
+    for (int j = 0; j < 4; j++) {
 #pragma unroll
       for (int e = 0; e < 4; e++) {
         float v = s[j][e] * scale_log2;
         if (need_mask) {
-          int const key = kt + j * 8 + 2 * tq + (e & 1);
+          int const key = kt + kh * 32 + j * 8 + 2 * tq + (e & 1);
           int const kvl = e < 2 ? kvlA : kvlB;
           int const bit = e < 2 ? bitA : bitB;
           bool vis = key < kvl && key < k1;
@@ -261,7 +262,7 @@ multi_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache, T 
     mB = mBn;
     float sumA = 0.f, sumB = 0.f;
 #pragma unroll
-    for (int j = 0; j < 8; j++) {
+    for (int j = 0; j < 4; j++) {
       s[j][0] = ex2(s[j][0] - bA);
       s[j][1] = ex2(s[j][1] - bA);
       s[j][2] = ex2(s[j][2] - bB);
@@ -278,9 +279,9 @@ multi_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache, T 
       o[j][2] *= cB;
       o[j][3] *= cB;
     }
-    // O += P V
+    // O += P V  (this warp's 32 keys)
 #pragma unroll
-    for (int kk = 0; kk < 4; kk++) {
+    for (int kk = 0; kk < 2; kk++) {
       uint32_t const a0 = DT<T>::pack(s[2 * kk][0], s[2 * kk][1]);
       uint32_t const a1 = DT<T>::pack(s[2 * kk][2], s[2 * kk][3]);
       uint32_t const a2 = DT<T>::pack(s[2 * kk + 1][0], s[2 * kk + 1][1]);
@@ -288,7 +289,7 @@ multi_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache, T 
 #pragma unroll
       for (int dp = 0; dp < DH / 16; dp++) {
         uint32_t b0, b1, b2, b3;
-        ldsm_x4_t(sVb + swz<DH>(kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, dp * 2 + (lane >> 4)), b0, b1, b2, b3);
+        ldsm_x4_t(sVb + swz<DH>(kh * 32 + kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, dp * 2 + (lane >> 4)), b0, b1, b2, b3);
         mma16816<T>(o[2 * dp], a0, a1, a2, a3, b0, b1);
         mma16816<T>(o[2 * dp + 1], a0, a1, a2, a3, b2, b3);
       }
@@ -296,6 +297,38 @@ multi_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache, T 
     __syncthreads(); // everyone is done with `buf` before it is refilled
   }
 
+  // merge the two key halves: thread (warp w+4, lane) hands its fragment-identical state to (warp w, lane)
+  {
+    constexpr int XW = DH / 2 + 4; // floats per thread: o fragment + mA, mB, lA, lB
+    float *xch = reinterpret_cast<float *>(sK) + ((size_t)rg * 32 + lane) * XW; // K tiles are dead after the loop's last barrier
+    if (kh == 1) {
+#pragma unroll
+      for (int j = 0; j < DH / 8; j++) {
+        *reinterpret_cast<float4 *>(xch + j * 4) = make_float4(o[j][0], o[j][1], o[j][2], o[j][3]);
+      }
+      *reinterpret_cast<float4 *>(xch + DH / 2) = make_float4(mA, mB, lA, lB);
+    }
+    __syncthreads();
+    if (kh == 1) {
+      return; // nothing after this point synchronises the whole block
+    }
+    float4 const st = *reinterpret_cast<float4 const *>(xch + DH / 2);
+    float const mAn = fmaxf(mA, st.x), mBn = fmaxf(mB, st.y);
+    float const c1A = mAn == -INFINITY ? 1.f : ex2(mA - mAn), c2A = mAn == -INFINITY ? 1.f : ex2(st.x - mAn);
+    float const c1B = mBn == -INFINITY ? 1.f : ex2(mB - mBn), c2B = mBn == -INFINITY ? 1.f : ex2(st.y - mBn);
+    lA = lA * c1A + st.z * c2A;
+    lB = lB * c1B + st.w * c2B;
+    mA = mAn;
+    mB = mBn;
+#pragma unroll
+    for (int j = 0; j < DH / 8; j++) {
+      float4 const v = *reinterpret_cast<float4 const *>(xch + j * 4);
+      o[j][0] = o[j][0] * c1A + v.x * c2A;
+      o[j][1] = o[j][1] * c1A + v.y * c2A;
+      o[j][2] = o[j][2] * c1B + v.z * c2B;
+      o[j][3] = o[j][3] * c1B + v.w * c2B;
+    }
+  }
   lA += __shfl_xor_sync(0xffffffffu, lA, 1);
   lA += __shfl_xor_sync(0xffffffffu, lA, 2);
   lB += __shfl_xor_sync(0xffffffffu, lB, 1);
@@ -339,7 +372,7 @@ multi_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache, T 
       // per-row arrival counters: the last split to finish a (token, head) row merges its records
       __shared__ int s_rowlast[BM];
       __threadfence();
-      __syncthreads();
+      asm volatile("bar.sync 2, 128;" ::: "memory"); // only the 4 surviving warps
       if (tid < BM) {
         int const th = s_tok[tid];
         int last = 0;
@@ -353,9 +386,9 @@ multi_attn_kernel(T const *__restrict__ q_buf, T const *__restrict__ k_cache, T 
         }
         s_rowlast[tid] = last;
       }
-      __syncthreads();
+      asm volatile("bar.sync 2, 128;" ::: "memory");
       __threadfence();
-      for (int r = warp; r < BM; r += MQ_THREADS / 32) {
+      for (int r = warp; r < BM; r += 4) {
         if (s_rowlast[r]) {
           int const th = s_tok[r];
           int const nvalid = min(nsplit, (s_kvlen[r] + chunk - 1) / chunk);

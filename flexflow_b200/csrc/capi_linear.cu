@@ -10,6 +10,10 @@
 namespace ffb {
 int launch_linear_stream(int dtype, int quant, void const *in, void *out, void const *w, void const *bias, int M,
                          int K, int N, cudaStream_t s);
+// persistent bulk-copy weight stream for decode batches (linear_gemv.cu)
+int linear_gemv_supported(int quant, int M, int K, int N);
+int launch_linear_gemv(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N,
+                       cudaStream_t s);
 // tcgen05/TMA GEMM for batched prompt/tree tokens (linear_tc.cu)
 int linear_tc_supported(int dtype, int quant, int K, int N);
 int launch_linear_tc(struct LinearTcState *st, int dtype, int quant, void const *in, void *out, void const *w,
@@ -89,6 +93,10 @@ int ffb_linear_forward(ffb_linear_t h, void const *in, void *out, void const *w,
   }
   if (use_tc) {
     return launch_linear_tc(h->tc, d.dtype, d.quant_type, in, out, w, bias, batch, d.in_dim, d.out_dim, s);
+  }
+  bool const force_stream = force && strcmp(force, "stream") == 0;
+  if (!force_stream && linear_gemv_supported(d.quant_type, batch, d.in_dim, d.out_dim)) {
+    return launch_linear_gemv(d.dtype, in, out, w, bias, batch, d.in_dim, d.out_dim, s);
   }
   size_t const elt = 2;
   for (int m0 = 0; m0 < batch; m0 += 64) {

@@ -96,6 +96,34 @@ def test_linear_stream(dtype, quant, M, monkeypatch):
     assert np.abs(got - want).max() <= tol * max(1.0, np.abs(want).max())
 
 
+@pytest.mark.parametrize("dtype", ["half", "bf16"])
+@pytest.mark.parametrize("M,K,N", [(1, 1024, 512), (7, 2048, 1536), (16, 4096, 2048), (16, 4096, 32 * 149)])
+def test_linear_gemv_decode(dtype, M, K, N):
+    """Default decode path (M <= 16, DT weights): persistent bulk-copy weight stream."""
+    torch = _torch()
+    from flexflow_b200 import ops
+    tdt = torch.float16 if dtype == "half" else torch.bfloat16
+    rng = np.random.default_rng(23)
+    x = O.round_to_dt(rng.standard_normal((M, K)).astype(np.float32), dtype)
+    w = O.round_to_dt((rng.standard_normal((N, K)) * 0.05).astype(np.float32), dtype)
+    b = O.round_to_dt(rng.standard_normal(N).astype(np.float32), dtype)
+    h = ops.FFHandler("cuda:0")
+    N32 = N  # out_dim % 32 is required by ffb_linear_create
+    if N % 32:
+        pytest.skip("out_dim must be a multiple of 32")
+    m = ops.LinearMeta(h, K, N32, dtype=tdt, max_tokens_per_batch=16)
+    out = torch.full((M, N), float("nan"), dtype=tdt, device="cuda")
+    for _ in range(2):  # twice: the ring/barrier state must be clean across launches
+        ops.Linear.inference_kernel_wrapper(m, None, torch.from_numpy(x).to("cuda", tdt), out,
+                                            torch.from_numpy(w).to("cuda", tdt), torch.from_numpy(b).to("cuda", tdt), K, N, M)
+    torch.cuda.synchronize()
+    want = O.linear(x, w, b, dtype)
+    got = out.float().cpu().numpy()
+    assert np.isfinite(got).all()
+    tol = 2e-3 if dtype == "half" else 1.2e-2
+    assert np.abs(got - want).max() <= tol * max(1.0, np.abs(want).max())
+
+
 def test_linear_bias_and_errors():
     torch = _torch()
     from flexflow_b200 import ops

@@ -69,7 +69,8 @@ def main():
     def decode7b():
         lens = {s: 2047 for s in range(16)}
         return TL.make_inc_batch([dict(slot=s, first_depth=2047, ntok=1) for s in range(16)]), lens
-    res.append(run("cfg2 7B decode b16 ctx2048", B.INC_DECODING_MODE, 32, 32, 128, decode7b, 16, 2048, 16))
+    if only != "cfg4":
+        res.append(run("cfg2 7B decode b16 ctx2048", B.INC_DECODING_MODE, 32, 32, 128, decode7b, 16, 2048, 16))
     if only == "cfg2":
         return
 
@@ -78,7 +79,11 @@ def main():
             lens = {s: 1024 for s in range(8)}
             return TL.make_tree_batch([dict(slot=s, committed_len=1024, parent=TL.random_tree(rng, ntree)) for s in range(8)]), lens
         return f
+    if only != "cfg4" or True:
+        pass
     res.append(run("cfg4 7B tree-verify b8 x64 ctx1024", B.TREE_VERIFY_MODE, 32, 32, 128, tree7b(64), 8, 1100, 512))
+    if only == "cfg4":
+        return
     res.append(run("cfg4' 7B tree-verify b8 x25 ctx1024 (reference max tree)", B.TREE_VERIFY_MODE, 32, 32, 128, tree7b(25), 8, 1100, 512))
 
     def tree70b():

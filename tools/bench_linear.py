@@ -12,13 +12,20 @@ from flexflow_b200 import ops  # noqa: E402
 
 
 def time_ms(fn, iters=20, warm=3):
+    """CUDA-graph replay of `iters` back-to-back calls (removes the Python/ctypes launch cost, which is
+    larger than these kernels), timed with CUDA events."""
     for _ in range(warm):
         fn()
     torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(iters):
+            fn()
+    g.replay()
+    torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(iters):
-        fn()
+    g.replay()
     e1.record()
     torch.cuda.synchronize()
     return e0.elapsed_time(e1) / iters
