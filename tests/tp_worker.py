@@ -1,0 +1,75 @@
+"""Worker for test_gpu_tp.py / the gloo CPU test: builds one attention block with FFModel at TP = world size and
+compares with the unsharded oracle-free reference computed by rank 0 at TP = 1 on the same weights."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import ffb_testlib as TL  # noqa: E402
+from flexflow_b200 import ops  # noqa: E402
+from flexflow_b200.model import FFConfig, FFModel  # noqa: E402
+from flexflow_b200.sharding import shard_o_proj, shard_qkv_proj  # noqa: E402
+
+HIDDEN, NQ, NKV, DH = 1024, 8, 8, 128
+
+
+def build(tp, rank, comm, dev):
+    cfg = FFConfig(tensor_parallelism_degree=tp, tp_rank=rank, max_requests_per_batch=4, max_tokens_per_batch=64,
+                   max_sequence_length=256, device=dev)
+    m = FFModel(cfg, comm)
+    x = m.create_tensor(HIDDEN)
+    qkv = m.dense(x, 3 * (NQ // tp) * DH, name="layers.0.self_attn.qkv_proj")
+    a = m.inc_multiquery_self_attention(qkv, HIDDEN, NQ, NKV, rotary_embedding_meta=ops.RotaryEmbeddingMeta(True),
+                                        name="layers.0.self_attn")
+    m.dense(a, HIDDEN, name="layers.0.self_attn.o_proj")
+    m.compile_inference()
+    return m, x
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(rank)
+    dev = "cuda:%d" % rank
+    dist.init_process_group("nccl", device_id=torch.device(dev))
+
+    def bcast(b):
+        o = [b]
+        dist.broadcast_object_list(o, src=0)
+        return o[0]
+    comm = ops.Communicator(rank, world, bcast)
+    g = torch.Generator().manual_seed(5)
+    wq = (torch.randn(NQ * DH, HIDDEN, generator=g) * 0.03).half()
+    wk = (torch.randn(NKV * DH, HIDDEN, generator=g) * 0.03).half()
+    wv = (torch.randn(NKV * DH, HIDDEN, generator=g) * 0.03).half()
+    wo = (torch.randn(HIDDEN, NQ * DH, generator=g) * 0.03).half()
+    hidden = torch.randn(12, HIDDEN, generator=g).half()
+    bc = TL.make_inc_batch([dict(slot=0, first_depth=0, ntok=9, prompt=True), dict(slot=2, first_depth=0, ntok=3, prompt=True)])
+    outs = []
+    for tp, r, c in ((world, rank, comm), (1, 0, None)):
+        m, x = build(tp, r, c, dev)
+        m.set_weight("layers.0.self_attn.qkv_proj", shard_qkv_proj(wq, wk, wv, NQ, NKV, DH, tp, r).to(dev))
+        m.set_weight("layers.0.self_attn.o_proj", shard_o_proj(wo, NQ, DH, tp, r).to(dev))
+        buf = torch.zeros(64, HIDDEN, dtype=torch.float16, device=dev)
+        buf[:12] = hidden.to(dev)
+        y = m.inference(bc, x, buf)
+        # decode one more token per request on top of the prompt KV
+        bc2 = TL.make_inc_batch([dict(slot=0, first_depth=9, ntok=1), dict(slot=2, first_depth=3, ntok=1)])
+        y2 = m.inference(bc2, x, buf)
+        torch.cuda.synchronize()
+        outs.append((y.float().cpu().numpy().copy(), y2.float().cpu().numpy().copy()))
+    for a, b in zip(outs[0], outs[1]):
+        err = np.abs(a - b).max() / max(np.abs(b).max(), 1e-6)
+        assert err < 1e-2, err
+    dist.barrier()
+    if rank == 0:
+        print("TP_OK")
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
