@@ -15,6 +15,7 @@ SOURCES = [
     "attn_prep.cu",
     "attn_decode.cu",
     "attn_multi.cu",
+    "attn_tc.cu",
     "capi_attn.cu",
     "dequant.cu",
     "linear_stream.cu",

@@ -25,6 +25,10 @@ struct ffb_attn_s {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int num_generation_tokens_cur = 0; // bc->num_generation_tokens of the batch in flight
   int num_active_infr_tokens = 0; // TreeIncMultiHeadSelfAttentionMeta::num_active_infr_tokens
+  // TMA descriptors (CUtensorMap, 128 bytes each) over the K and V caches viewed as [rows][head_dim] (attn_tc.cu)
+  alignas(64) unsigned char tmK[128];
+  alignas(64) unsigned char tmV[128];
+  bool tm_ready = false;
 };
 
 namespace ffb {
@@ -42,6 +46,11 @@ int launch_decode_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta
 // multi-query (tree / beam / prompt / GQA) attention
 int launch_multi_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, void *out, int T,
                       int kv_len_max, int q_len_max, cudaStream_t s);
+// tcgen05 / TMA version of the multi-query kernel (attn_tc.cu)
+int attn_tc_init(ffb_attn_s *h);
+int attn_tc_supported(ffb_attn_s *h);
+int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, void *out, int T,
+                   int kv_len_max, int q_len_max, cudaStream_t s);
 int launch_kv_io(ffb_attn_s *h, int request, int pos0, int n, void *k, void *v, bool write,
                  cudaStream_t s);
 

@@ -44,6 +44,18 @@ int ffb_check_device(void) {
   return FFB_OK;
 }
 
+// Multi-query attention: the tcgen05 / TMA kernel (attn_tc.cu) by default; FFB_ATTN_TC=0 selects the mma.sync
+// kernel (attn_multi.cu), kept as the in-tree comparison point.
+static int launch_multi_dispatch(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, void *out, int T,
+                                 int kv_len_max, int q_len_max, cudaStream_t s) {
+  char const *e = getenv("FFB_ATTN_TC");
+  bool const want_tc = !(e && e[0] == '0');
+  if (want_tc && attn_tc_supported(h)) {
+    return launch_attn_tc(h, meta, out, T, kv_len_max, q_len_max, s);
+  }
+  return launch_multi_attn(h, meta, out, T, kv_len_max, q_len_max, s);
+}
+
 int ffb_attn_create(ffb_attn_desc const *desc, ffb_attn_t *out) {
   FFB_REQUIRE(desc && out, "null argument");
   ffb_attn_desc const &d = *desc;
@@ -110,6 +122,12 @@ int ffb_attn_create(ffb_attn_desc const *desc, ffb_attn_t *out) {
     cudaFree(h->base);
     delete h;
     return FFB_ERR_CUDA;
+  }
+  rc = attn_tc_init(h);
+  if (rc != FFB_OK) {
+    cudaFree(h->base);
+    delete h;
+    return rc;
   }
   *out = h;
   return FFB_OK;
@@ -247,7 +265,7 @@ int ffb_inc_attn_forward(ffb_attn_t h, ffb_batch_config const *bc, ffb_combined_
   int const force = forced_kernel();
   bool const use_decode = force == 1 || (force == 0 && !sc.any_multi && h->G == 1);
   return use_decode ? launch_decode_attn(h, meta, out, T, sc.kv_len_max, s)
-                    : launch_multi_attn(h, meta, out, T, sc.kv_len_max, sc.q_len_max, s);
+                    : launch_multi_dispatch(h, meta, out, T, sc.kv_len_max, sc.q_len_max, s);
 }
 
 int ffb_tree_attn_forward(ffb_attn_t h, ffb_tree_verify_batch_config const *tbc,
@@ -297,7 +315,7 @@ int ffb_tree_attn_forward(ffb_attn_t h, ffb_tree_verify_batch_config const *tbc,
   if (rc != FFB_OK) {
     return rc;
   }
-  return launch_multi_attn(h, meta, out, T, sc.kv_len_max, sc.q_len_max, s);
+  return launch_multi_dispatch(h, meta, out, T, sc.kv_len_max, sc.q_len_max, s);
 }
 
 int ffb_spec_attn_forward(ffb_attn_t h, ffb_beam_search_batch_config const *bbc,
@@ -334,7 +352,7 @@ int ffb_spec_attn_forward(ffb_attn_t h, ffb_beam_search_batch_config const *bbc,
   if (rc != FFB_OK) {
     return rc;
   }
-  return launch_multi_attn(h, meta, out, T, sc.kv_len_max, sc.q_len_max, s);
+  return launch_multi_dispatch(h, meta, out, T, sc.kv_len_max, sc.q_len_max, s);
 }
 
 int ffb_attn_read_kv(ffb_attn_t h, int request, int pos0, int n, void *k, void *v, ffb_stream_t stream) {

@@ -15,69 +15,16 @@
 #include <new>
 #include <type_traits>
 
-#include "common.cuh"
+#include "tc_common.cuh"
 
 extern "C" int ffb_dequant_int4(void const *, void *, int, int, int, ffb_stream_t);
 extern "C" int ffb_dequant_int8(void const *, void *, int, int, int, ffb_stream_t);
 
 namespace ffb {
+using namespace tc;
 namespace {
 
 constexpr int TC_BM = 128, TC_BK = 64, TC_THREADS = 256;
-
-__device__ __forceinline__ uint32_t smem_u32(void const *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
-  uint32_t const addr = smem_u32(bar);
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "WAIT_LOOP:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra DONE;\n\t"
-      "bra WAIT_LOOP;\n\t"
-      "DONE:\n\t"
-      "}" ::"r"(addr), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(void *dst, CUtensorMap const *tm, int c0, int c1, uint64_t *bar) {
-  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-               ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint64_t *bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
-      "}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
-}
-// K-major operand tile, 128-byte swizzle: rows of 128 B, 8-row groups 1024 B apart
-// (cute::UMMA::SmemDescriptor: start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48), layout [61,64))
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
-  return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
 
 template <typename T, int BN, int STAGES>
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -201,8 +148,10 @@ EncodeTiledFn encode_fn() {
   return fn;
 }
 
+} // namespace
+
 // [rows][K] row-major 16-bit matrix, box = 64 (K) x box_rows, 128B swizzle, OOB rows read as zero
-int make_map(CUtensorMap *tm, int dtype, void const *ptr, int rows, int K, int box_rows) {
+int make_tensor_map_2d(CUtensorMap *tm, int dtype, void const *ptr, long rows, int K, int box_rows) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled is not available from the driver");
@@ -216,13 +165,12 @@ int make_map(CUtensorMap *tm, int dtype, void const *ptr, int rows, int K, int b
                   (void *)ptr, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
-    set_error("cuTensorMapEncodeTiled failed with CUresult %d (ptr %p rows %d K %d)", (int)r, ptr, rows, K);
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d (ptr %p rows %ld K %d)", (int)r, ptr, rows, K);
     return FFB_ERR_CUDA;
   }
   return FFB_OK;
 }
 
-} // namespace
 
 struct LinearTcState {
   int dtype, quant, K, N, max_batch;
@@ -278,11 +226,11 @@ int launch_linear_tc(LinearTcState *st, int dtype, int quant, void const *in, vo
   }
   constexpr int BN = 128, STAGES = 6;
   CUtensorMap tmA, tmB;
-  int rc = make_map(&tmA, dtype, in, M, K, TC_BM);
+  int rc = make_tensor_map_2d(&tmA, dtype, in, M, K, TC_BM);
   if (rc != FFB_OK) {
     return rc;
   }
-  rc = make_map(&tmB, dtype, wd, N, K, BN);
+  rc = make_tensor_map_2d(&tmB, dtype, wd, N, K, BN);
   if (rc != FFB_OK) {
     return rc;
   }
