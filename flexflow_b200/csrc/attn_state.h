@@ -49,8 +49,15 @@ int launch_multi_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta,
 // tcgen05 / TMA version of the multi-query kernel (attn_tc.cu)
 int attn_tc_init(ffb_attn_s *h);
 int attn_tc_supported(ffb_attn_s *h);
-int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, void *out, int T,
-                   int kv_len_max, int q_len_max, cudaStream_t s);
+// one active request as the host sees it (from the BatchConfig), input of the tcgen05 kernel's stream-K schedule
+struct AtcReq {
+  int slot, first_tok, qlen; // request slot, first_token_offset_in_batch, query tokens in this batch
+  int tl;                    // keys visible to the request's last query token
+  int ntcs;                  // causalMask[slot].non_tree_cache_size
+  int causal, first_depth;   // causal != 0: token qi sees keys [0, first_depth + qi + 1)
+};
+int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, void *out, int T, AtcReq const *reqs,
+                   int nreq, cudaStream_t s);
 int launch_kv_io(ffb_attn_s *h, int request, int pos0, int n, void *k, void *v, bool write,
                  cudaStream_t s);
 

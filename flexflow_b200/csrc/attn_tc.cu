@@ -4,27 +4,32 @@
 // compute_spec_inc_attention_kernel_generation_kernel (src/ops/spec_inc_multihead_self_attention.cu:36-309)
 // and the cuBLAS + cuDNN prompt path (src/ops/inc_multihead_self_attention.cu:98-366).
 //
-// One CTA owns a 128-row query tile (query tokens x the q heads sharing one kv head) of one request and a
-// key range of the split; every K/V tile of 128 keys is read from HBM exactly once:
+// PERSISTENT, one CTA per SM.  A work unit is a 128-row query tile (query tokens x the q heads sharing one kv
+// head) of one request; its K/V is cut into 128-key tiles.  The host flattens all (unit, key tile) pairs of the
+// batch and gives every CTA one contiguous range of that list (stream-K), so the SMs finish together whatever
+// the request lengths are; a unit that straddles CTAs is merged through split records (exact log-sum-exp merge
+// by the last CTA to finish the row, combine_record).  Every K/V tile is read from HBM exactly once:
 //   warp 8 (one lane)  TMA producer: K and V tiles straight from the [request][kv_head][cache_len][Dh] cache into
-//                      128B-swizzled shared-memory rings (separate full/empty mbarriers for K and V)
-//   warp 9 (one lane)  MMA issuer: S = Q K^T (UMMA 128x128x16, both operands K-major) into one of two TMEM
-//                      score buffers, then O += P V (V consumed MN-major, exactly as TMA laid it down) into the
-//                      TMEM output accumulator; tcgen05.commit releases ring slots
+//                      a 192 KB ring of 128B-swizzled buffers (K0 V0 K1 V1 ...); it runs ahead across unit
+//                      boundaries, so the HBM stream never drains while a unit's epilogue / the next Q load runs
+//   warp 9 (one lane)  MMA issuer: S = Q K^T (UMMA 128x128x16, Q from TENSOR MEMORY, K from smem K-major) into one
+//                      of two TMEM score buffers, then O += P V (P from tensor memory - it overwrites the first
+//                      64 columns of its own score buffer - and V consumed MN-major exactly as TMA laid it down)
 //   warps 0-7          two threads per query row (warps w and w+4 share TMEM lane quarter w, each takes 64 of
 //                      the 128 keys and half of the output columns): tcgen05.ld the scores, scale + kv_len /
 //                      causal / tree-bit mask, online softmax in the log2 domain against a LAZY reference
 //                      maximum (the TMEM accumulator is rescaled only when a row maximum grows by more than
-//                      2^8, so P stays <= 256 and most tiles need no correction), P written 16-bit into
-//                      swizzled smem (A operand of the second MMA)
-// The softmax of tile j overlaps the QK^T MMA of tile j+1; the kernel is HBM-bound: 64 KB of K/V
-// per tile per SM (~2900 cycles at the HBM rate) against ~1000 tensor-pipe and ~1000 MUFU cycles.
+//                      2^8, so P stays <= 256 and most tiles need no correction), P back into TMEM (tcgen05.st)
+// Shared memory holds nothing but the K/V stream.  HBM-bound: 64 KB of K/V per tile per SM
+// (~2900 cycles at the HBM rate) against ~1000 tensor-pipe and ~1000 MUFU cycles.
+#include <algorithm>
+#include <cstdio>
+#include <type_traits>
+
 #include "attn_state.h"
 #include "tc_common.cuh"
 
 namespace ffb {
-
-int launch_combine(ffb_attn_s *h, void *out, int T, int chunk, int nsplit, cudaStream_t s);
 
 using namespace tc;
 
@@ -32,434 +37,571 @@ namespace {
 
 constexpr int TBM = 128, TBN = 128, ATC_SOFTMAX_THREADS = 256, ATC_THREADS = 320;
 constexpr float kRescaleThreshold = 8.f; // log2 domain
+constexpr int ATC_MAX_ENT = 128;
+
+// One entry per (request, 128-row query tile); it stands for num_kv_heads units of `ntiles` key tiles each.
+// Flattened tile index of (entry e, kv head h, tile t) = cum[e] + h * ntiles[e] + t.
+struct AtcEntry {
+  int cum;        // flattened index of this entry's first tile
+  int first_tok;  // first_token_offset_in_batch of the request
+  int ntcs;       // causalMask[slot].non_tree_cache_size
+  short slot, mt; // request slot, row-tile index inside the request
+  short ntiles;   // key tiles of 128 covering the longest row of the tile
+  short qlen;     // query tokens of the request in this batch
+};
+struct AtcSched {
+  int n_ent;     // entries in use
+  int total;     // total flattened tiles
+  int rg;        // tiles per CTA (CTA c owns [c*rg, min(total, (c+1)*rg)))
+  int maxpieces; // stride of the split records of one (token, head)
+  AtcEntry ent[ATC_MAX_ENT];
+};
 
 template <int DH> struct AtcCfg {
-  static constexpr int KH = DH / 64;                 // 64-element (128-byte) column blocks per row
-  static constexpr int STAGES = DH == 128 ? 2 : 4;   // K and V ring depth
-  static constexpr uint32_t HALF_BYTES = 128 * 128;  // one [128 rows][64 cols] swizzled block
-  static constexpr uint32_t Q_BYTES = KH * HALF_BYTES;
-  static constexpr uint32_t P_BYTES = 2 * HALF_BYTES;
-  static constexpr uint32_t KV_BYTES = KH * HALF_BYTES;
-  static constexpr size_t SMEM = Q_BYTES + P_BYTES + 2 * STAGES * KV_BYTES + 1024;
+  static constexpr int KH = DH / 64;                    // 64-element (128-byte) column blocks per row
+  static constexpr uint32_t HALF_BYTES = 128 * 128;     // one [128 keys][64 cols] swizzled block
+  static constexpr uint32_t KV_BYTES = KH * HALF_BYTES; // one K tile or one V tile
+  static constexpr int NBUF = (192 * 1024) / KV_BYTES;  // ring slots; K and V tiles alternate: K0 V0 K1 V1 ...
+  static constexpr size_t SMEM = (size_t)NBUF * KV_BYTES + 1024;
+};
+
+// Walks the segments of one CTA: maximal runs of consecutive flattened tiles inside one unit.
+struct SegWalk {
+  int x, x_end; // flattened position, end of this CTA's range
+  int e;        // entry cursor
+  // current segment
+  int kvh, t0, t1;
+  __device__ __forceinline__ void init(AtcSched const &sc) {
+    x = (int)blockIdx.x * sc.rg;
+    x_end = min(sc.total, x + sc.rg);
+    e = 0;
+  }
+  __device__ __forceinline__ bool next(AtcSched const &sc) {
+    if (x >= x_end) {
+      return false;
+    }
+    while (e + 1 < sc.n_ent && sc.ent[e + 1].cum <= x) {
+      e++;
+    }
+    int const nt = sc.ent[e].ntiles;
+    int const r = x - sc.ent[e].cum;
+    kvh = r / nt;
+    t0 = r - kvh * nt;
+    t1 = min(nt, t0 + (x_end - x));
+    x += t1 - t0;
+    return true;
+  }
 };
 
 template <typename T, int DH>
+// 10 warps are allocated as 12 (warp allocation granularity 4): 65536 / 384 = 170 registers per thread at most
 __global__ void __launch_bounds__(ATC_THREADS, 1)
 attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
-               T const *__restrict__ q_buf, QueryDesc const *__restrict__ qdesc,
-               ffb_combined_batch_config_meta const *__restrict__ meta, float *__restrict__ partial,
-               int *__restrict__ split_counter, T *__restrict__ out, int mode, int nq, int nkv, int cache_len,
-               int m_tiles, int chunk, int nsplit, float scale_log2, int num_generation_tokens, int fuse_combine) {
+               const __grid_constant__ AtcSched sched, T const *__restrict__ q_buf,
+               QueryDesc const *__restrict__ qdesc, ffb_combined_batch_config_meta const *__restrict__ meta,
+               float *__restrict__ partial, int *__restrict__ split_counter, T *__restrict__ out, int nq, int nkv,
+               int cache_len, float scale_log2, long long *trace) {
   using Cfg = AtcCfg<DH>;
-  constexpr int KH = Cfg::KH, STAGES = Cfg::STAGES;
+  constexpr int KH = Cfg::KH, NBUF = Cfg::NBUF;
   constexpr uint32_t HALF = Cfg::HALF_BYTES;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t k_full[STAGES], k_empty[STAGES], v_full[STAGES], v_empty[STAGES];
-  __shared__ __align__(8) uint64_t s_full[2], s_empty[2], o_full, p_full;
+  __shared__ __align__(8) uint64_t kv_full[NBUF], kv_empty[NBUF];
+  __shared__ __align__(8) uint64_t s_full[2], o_full, p_full, q_full;
   __shared__ float s_xch[2][2][TBM]; // [tile parity][column half][row]: partial row maxima / final row sums
   __shared__ uint32_t tmem_base_smem;
-  __shared__ int s_kvlen[TBM], s_bit[TBM], s_tok[TBM], s_rowlast[TBM];
-  __shared__ unsigned long long s_mask[64];
-  __shared__ int s_hi, s_lo, s_anybit;
+  __shared__ int s_rowlast[TBM];
+  __shared__ unsigned long long s_mask[2][64]; // tree bit masks of the current / next segment's request
 
-  int const slot = blockIdx.z;
-  if (meta->request_completed[slot]) {
-    return;
-  }
-  ffb_per_request_info const *ri = &meta->requestsInfo[slot];
-  int const first_tok = ri->first_token_offset_in_batch;
-  int qlen = ri->num_tokens_in_batch;
-  if (mode == FFB_BEAM_SEARCH_MODE && first_tok < num_generation_tokens) {
-    qlen = meta->beamRequestsInfo[slot].sub_request_num; // spec_…cu:97-98
-  }
-  int const G = nq / nkv;
-  int const kvh = blockIdx.y / m_tiles, mt = blockIdx.y % m_tiles;
-  int const rows_total = qlen * G;
-  if (mt * TBM >= rows_total) {
-    return;
-  }
-  int const split = blockIdx.x, k0 = split * chunk;
   int const tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  int const ntcs = meta->causalMask[slot].non_tree_cache_size;
-
-  if (tid == 0) {
-    s_hi = 0;
-    s_lo = 0x7fffffff;
-    s_anybit = 0;
-  }
-  if (tid >= 256) {
-    s_mask[tid - 256] = meta->causalMask[slot].mask[tid - 256];
-  }
-  __syncthreads();
-  if (tid < TBM) {
-    int const R = mt * TBM + tid;
-    int tokhead = -1, kvl = 0, bit = -1;
-    if (R < rows_total) {
-      int const tok = first_tok + R / G;
-      tokhead = tok * nq + kvh * G + R % G;
-      QueryDesc const qd = qdesc[tok];
-      kvl = qd.kv_len;
-      bit = qd.bit;
-      atomicMax(&s_hi, kvl);
-      atomicMin(&s_lo, kvl);
-      if (bit >= 0) {
-        atomicOr(&s_anybit, 1);
-      }
+  int const G = nq / nkv;
+#ifdef FFB_ATC_TRACE_BUILD
+  // nvcc -DFFB_ATC_TRACE_BUILD + env FFB_ATC_TRACE=<n>: CTA 0 records (event id, globaltimer) pairs of its n-th launch;
+  // role r (0 producer, 1 MMA issuer, 2 softmax thread 0) writes into trace[r*512 ...]
+  int tr_n = 0;
+  auto tr = [&](int role, int ev) {
+    if (trace && blockIdx.x == 0 && tr_n < 255) {
+      long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      trace[role * 512 + 2 * tr_n] = ev;
+      trace[role * 512 + 2 * tr_n + 1] = t;
+      tr_n++;
     }
-    s_tok[tid] = tokhead;
-    s_kvlen[tid] = kvl;
-    s_bit[tid] = bit;
-  }
-  __syncthreads();
-  int const kv_hi = s_hi, kv_lo = s_lo;
-  bool const anybit = s_anybit != 0;
-  if (split == 0 && kv_lo <= 0 && tid < TBM) { // rows without any key: zero output (no split will touch them)
-    if (s_tok[tid] >= 0 && s_kvlen[tid] <= 0) {
-      uint4 *dst = reinterpret_cast<uint4 *>(out + (size_t)s_tok[tid] * DH);
-      for (int c = 0; c < DH / 8; c++) {
-        dst[c] = make_uint4(0u, 0u, 0u, 0u);
-      }
-    }
-  }
-  if (k0 >= kv_hi) {
-    return;
-  }
-  int const k1 = min(k0 + chunk, kv_hi);
-  int const ntiles = (k1 - k0 + TBN - 1) / TBN;
-
+  };
+#define FFB_TR(role, ev) tr(role, ev)
+#else
+#define FFB_TR(role, ev) ((void)0)
+#endif
   // 128B-swizzled operand blocks need 1024-byte alignment
-  uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-  uint8_t *sQ = smem, *sP = sQ + Cfg::Q_BYTES, *sK = sP + Cfg::P_BYTES, *sV = sK + STAGES * Cfg::KV_BYTES;
+  uint8_t *sKV = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
 
-  if (warp == 9 && lane == 0) {
-    for (int s = 0; s < STAGES; s++) {
-      mbar_init(&k_full[s], 1);
-      mbar_init(&k_empty[s], 1);
-      mbar_init(&v_full[s], 1);
-      mbar_init(&v_empty[s], 1);
-    }
-    for (int b = 0; b < 2; b++) {
-      mbar_init(&s_full[b], 1);
-      mbar_init(&s_empty[b], ATC_SOFTMAX_THREADS);
-    }
-    mbar_init(&o_full, 1);
-    mbar_init(&p_full, ATC_SOFTMAX_THREADS);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  if (warp == 8) { // TMEM: 2 score buffers + the output accumulator, 128 fp32 columns each (512 allocated)
+  if (warp == 8) {
+    // ===== TMA producer =====  (never waits for the rest of the CTA: the stream starts at once)
     if (lane == 0) {
+      for (int sb = 0; sb < NBUF; sb++) {
+        mbar_init(&kv_full[sb], 1);
+        mbar_init(&kv_empty[sb], 1);
+      }
+      mbar_init(&s_full[0], 1);
+      mbar_init(&s_full[1], 1);
+      mbar_init(&o_full, 1);
+      mbar_init(&p_full, ATC_SOFTMAX_THREADS);
+      mbar_init(&q_full, ATC_SOFTMAX_THREADS);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(&tmK) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(&tmV) : "memory");
     }
     __syncwarp();
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "r"(512u));
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
-  }
-  if (tid < TBM) { // Q tile: row `tid`, zero-filled past the request's queries, written in the swizzled K-major layout
-    int const th = s_tok[tid];
-    uint4 const *src = reinterpret_cast<uint4 const *>(q_buf + (size_t)(th >= 0 ? th : 0) * DH);
-#pragma unroll
-    for (int c = 0; c < DH / 8; c++) {
-      uint4 const v = th >= 0 ? src[c] : make_uint4(0u, 0u, 0u, 0u);
-      *reinterpret_cast<uint4 *>(sQ + (c >> 3) * HALF + tid * 128 + (((c & 7) ^ (tid & 7)) << 4)) = v;
-    }
-    fence_proxy_async();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  uint32_t const tmem_base = tmem_base_smem;
-  uint32_t const tmem_S = tmem_base, tmem_O = tmem_base + 256;
-  int const row_base = (slot * nkv + kvh) * cache_len; // first cache row of this (request, kv head)
-
-  if (warp == 8) {
+    asm volatile("barrier.cta.arrive 0, %0;" ::"n"(ATC_THREADS) : "memory");
     if (lane == 0) {
-      // ===== TMA producer =====
-      for (int it = 0; it < ntiles; it++) {
-        int const s = it % STAGES;
-        uint32_t const ph = (it / STAGES) & 1;
-        int const r0 = row_base + k0 + it * TBN;
-        mbar_wait(&k_empty[s], ph ^ 1);
-        mbar_expect_tx(&k_full[s], Cfg::KV_BYTES);
+      SegWalk w;
+      w.init(sched);
+      int j = 0; // ring item counter: K tile, V tile, K tile, ...
+      while (w.next(sched)) {
+        int const row_base = ((int)sched.ent[w.e].slot * nkv + w.kvh) * cache_len;
+        for (int t = w.t0; t < w.t1; t++) {
 #pragma unroll
-        for (int hh = 0; hh < KH; hh++) {
-          tma_load_2d(sK + s * Cfg::KV_BYTES + hh * HALF, &tmK, hh * 64, r0, &k_full[s]);
-        }
-        mbar_wait(&v_empty[s], ph ^ 1);
-        mbar_expect_tx(&v_full[s], Cfg::KV_BYTES);
+          for (int kv = 0; kv < 2; kv++, j++) {
+            int const sb = j % NBUF;
+            mbar_wait(&kv_empty[sb], ((j / NBUF) & 1) ^ 1);
+            FFB_TR(0, j);
+            mbar_expect_tx(&kv_full[sb], Cfg::KV_BYTES);
 #pragma unroll
-        for (int hh = 0; hh < KH; hh++) {
-          tma_load_2d(sV + s * Cfg::KV_BYTES + hh * HALF, &tmV, hh * 64, r0, &v_full[s]);
-        }
-      }
-    }
-  } else if (warp == 9) {
-    if (lane == 0) {
-      // ===== MMA issuer =====
-      // cute::UMMA::InstrDescriptor: c_format F32 (1) @4, a/b format @7/@10 (F16 0, BF16 1), b_major @16 (1 = MN-major),
-      // N>>3 @17, M>>4 @24
-      constexpr uint32_t fmt = std::is_same<T, __nv_bfloat16>::value ? 1u : 0u;
-      constexpr uint32_t idesc_qk = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(TBN >> 3) << 17) | ((uint32_t)(TBM >> 4) << 24);
-      constexpr uint32_t idesc_pv = (1u << 4) | (fmt << 7) | (fmt << 10) | (1u << 16) | ((uint32_t)(DH >> 3) << 17) | ((uint32_t)(TBM >> 4) << 24);
-      auto issue_qk = [&](int it) {
-        int const s = it % STAGES;
-        mbar_wait(&k_full[s], (it / STAGES) & 1);
-        tc_fence_after();
-        uint32_t const kb = smem_u32(sK + s * Cfg::KV_BYTES);
-#pragma unroll
-        for (int k = 0; k < DH / 16; k++) {
-          uint64_t const da = umma_desc_sw128(smem_u32(sQ) + (k >> 2) * HALF) + (uint64_t)((k & 3) * 2);
-          uint64_t const db = umma_desc_sw128(kb + (k >> 2) * HALF) + (uint64_t)((k & 3) * 2);
-          tc_mma_f16(tmem_S + (uint32_t)(it & 1) * 128u, da, db, idesc_qk, k != 0);
-        }
-        tc_commit(&k_empty[s]);
-        tc_commit(&s_full[it & 1]);
-      };
-      issue_qk(0);
-      if (ntiles > 1) {
-        issue_qk(1);
-      }
-      for (int it = 0; it < ntiles; it++) {
-        int const s = it % STAGES;
-        mbar_wait(&p_full, it & 1);
-        mbar_wait(&v_full[s], (it / STAGES) & 1);
-        tc_fence_after();
-        uint32_t const vb = smem_u32(sV + s * Cfg::KV_BYTES);
-#pragma unroll
-        for (int k = 0; k < TBN / 16; k++) {
-          uint64_t const da = umma_desc_sw128(smem_u32(sP) + (k >> 2) * HALF) + (uint64_t)((k & 3) * 2);
-          uint64_t const db = umma_desc_mn_sw128(vb + k * 2048, HALF, 1024);
-          tc_mma_f16(tmem_O, da, db, idesc_pv, (it | k) != 0);
-        }
-        tc_commit(&v_empty[s]);
-        tc_commit(&o_full);
-        if (it + 2 < ntiles) {
-          mbar_wait(&s_empty[it & 1], (it >> 1) & 1);
-          issue_qk(it + 2);
+            for (int hh = 0; hh < KH; hh++) {
+              tma_load_2d(sKV + sb * Cfg::KV_BYTES + hh * HALF, kv ? &tmV : &tmK, hh * 64, row_base + t * TBN, &kv_full[sb]);
+            }
+          }
         }
       }
     }
   } else {
-    // ===== softmax warps: threads (row, h) with h = warp / 4 own keys [64h, 64h+64) of every tile =====
-    int const row = tid & (TBM - 1), hc = tid >> 7;
-    int const kvl = s_kvlen[row], bit = s_bit[row];
-    int const th = s_tok[row];
-    bool const warp_active = __any_sync(0xffffffffu, th >= 0); // a warp of padding rows only keeps the barriers moving
-    uint32_t const lane_sel = (uint32_t)((warp & 3) * 32) << 16;
-    uint32_t const pair_bar = 1 + (warp & 3); // named barrier shared by warps w and w+4
-    constexpr int OC = DH / 2;                // output columns per thread
-    uint32_t const tO = tmem_O + lane_sel + (uint32_t)(hc * OC);
-    float m_ref = -INFINITY, l = 0.f;
-    uint8_t *prow = sP + hc * HALF + row * 128;
-    int const rx = row & 7;
-
-    for (int it = 0; it < ntiles; it++) {
-      int const b = it & 1;
-      int const kbase = k0 + it * TBN + hc * 64; // first key of this thread's 64 columns
-      uint32_t const tS = tmem_S + (uint32_t)b * 128u + lane_sel + (uint32_t)(hc * 64);
-      bool const need_mask = (kbase + 64 > kv_lo) || (kbase + 64 > k1) || (anybit && kbase + 64 > ntcs);
-      float sc[64];
-      mbar_wait(&s_full[b], (it >> 1) & 1);
-      tc_fence_after();
-      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
-      if (warp_active) {
-        uint32_t r0[32], r1[32];
-        tmem_ld32_nowait(tS, r0);
-        tmem_ld32_nowait(tS + 32u, r1);
-        tmem_ld_wait();
-#pragma unroll
-        for (int e = 0; e < 32; e++) {
-          sc[e] = __uint_as_float(r0[e]) * scale_log2;
-          sc[32 + e] = __uint_as_float(r1[e]) * scale_log2;
-        }
-        if (need_mask) {
-#pragma unroll
-          for (int e = 0; e < 64; e++) {
-            int const key = kbase + e;
-            bool vis = key < kvl && key < k1;
-            if (vis && bit >= 0 && key >= ntcs) {
-              int const idx = key - ntcs;
-              vis = idx < 64 && bit < 64 && ((s_mask[idx & 63] >> (bit & 63)) & 1ULL);
-            }
-            sc[e] = vis ? sc[e] : -INFINITY;
-          }
-        }
-#pragma unroll
-        for (int e = 0; e < 64; e += 4) {
-          mx0 = fmaxf(mx0, sc[e]);
-          mx1 = fmaxf(mx1, sc[e + 1]);
-          mx2 = fmaxf(mx2, sc[e + 2]);
-          mx3 = fmaxf(mx3, sc[e + 3]);
-        }
-      }
-      float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
-      s_xch[b][hc][row] = mx;
-      asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
-      mx = fmaxf(mx, s_xch[b][hc ^ 1][row]);
-      // lazy reference maximum: move it (and rescale the accumulator) only when the row maximum outgrows it by 2^8
-      bool const grow = mx > m_ref + kRescaleThreshold || (m_ref == -INFINITY && mx > -INFINITY);
-      float const alpha = grow ? (m_ref == -INFINITY ? 1.f : ffb_ex2(m_ref - mx)) : 1.f;
-      if (grow) {
-        m_ref = mx;
-      }
-      float const base = m_ref == -INFINITY ? 0.f : m_ref;
-      if (it > 0) { // the PV MMA of the previous tile has finished: P may be overwritten, O may be corrected
-        mbar_wait(&o_full, (it - 1) & 1);
-        tc_fence_after();
-        if (__any_sync(0xffffffffu, alpha != 1.f)) {
-#pragma unroll
-          for (int c = 0; c < OC / 32; c++) {
-            uint32_t r[32];
-            tmem_ld32(tO + (uint32_t)(c * 32), r);
-#pragma unroll
-            for (int e = 0; e < 32; e++) {
-              r[e] = __float_as_uint(__uint_as_float(r[e]) * alpha);
-            }
-            tmem_st32(tO + (uint32_t)(c * 32), r);
-          }
-          tmem_st_wait();
-        }
-      }
-      if (warp_active) {
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-#pragma unroll
-        for (int v4 = 0; v4 < 8; v4++) {
-          float f[8];
-#pragma unroll
-          for (int e = 0; e < 8; e++) {
-            f[e] = ffb_ex2(sc[v4 * 8 + e] - base);
-          }
-          s0 += f[0] + f[4];
-          s1 += f[1] + f[5];
-          s2 += f[2] + f[6];
-          s3 += f[3] + f[7];
-          *reinterpret_cast<uint4 *>(prow + ((v4 ^ rx) << 4)) = pack8<T>(f);
-        }
-        l = l * alpha + ((s0 + s1) + (s2 + s3));
-      }
-      tc_fence_before();
-      mbar_arrive(&s_empty[b]); // score buffer b may be overwritten by QK^T of tile it+2
-      fence_proxy_async();
-      mbar_arrive(&p_full);     // this thread's part of P (and of the corrected O) is in place
+    if (warp == 9) {
+      // TMEM: score buffers S0 S1 (P overwrites the first 64 columns of its S), output accumulator, Q operand
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "r"(512u));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
     }
-    // row sum over both column halves
-    s_xch[0][hc][row] = l;
-    mbar_wait(&o_full, (ntiles - 1) & 1);
+    tc_fence_before();
+    asm volatile("barrier.cta.sync 0, %0;" ::"n"(ATC_THREADS) : "memory");
     tc_fence_after();
-    asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
-    l += s_xch[0][hc ^ 1][row];
-    if (nsplit == 1) {
-      if (warp_active) {
-        float const inv = __fdividef(1.f, l + 1.e-6f);
-        uint4 *dst = reinterpret_cast<uint4 *>(out + (size_t)(th >= 0 ? th : 0) * DH + hc * OC);
+    uint32_t const tmem_base = tmem_base_smem;
+    uint32_t const tmem_S = tmem_base, tmem_O = tmem_base + 256, tmem_Q = tmem_base + 384;
+
+    if (warp == 9) {
+      if (lane == 0) {
+        // ===== MMA issuer =====
+        // cute::UMMA::InstrDescriptor: c_format F32 (1) @4, a/b format @7/@10 (F16 0, BF16 1), b_major @16
+        // (1 = MN-major), N>>3 @17, M>>4 @24.  The A operand (Q, then P) is in tensor memory: 8 columns per K=16 step.
+        constexpr uint32_t fmt = std::is_same<T, __nv_bfloat16>::value ? 1u : 0u;
+        constexpr uint32_t idesc_qk = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(TBN >> 3) << 17) | ((uint32_t)(TBM >> 4) << 24);
+        constexpr uint32_t idesc_pv = (1u << 4) | (fmt << 7) | (fmt << 10) | (1u << 16) | ((uint32_t)(DH >> 3) << 17) | ((uint32_t)(TBM >> 4) << 24);
+        auto issue_qk = [&](int g) { // g: CTA-wide tile counter
+          int const j = 2 * g, sb = j % NBUF;
+          mbar_wait(&kv_full[sb], (j / NBUF) & 1);
+          FFB_TR(1, 1000 + g);
+          tc_fence_after();
+          uint32_t const kb = smem_u32(sKV + sb * Cfg::KV_BYTES);
 #pragma unroll
-        for (int c = 0; c < OC / 32; c++) {
-          uint32_t r[32];
-          tmem_ld32(tO + (uint32_t)(c * 32), r);
-          if (th >= 0) {
+          for (int k = 0; k < DH / 16; k++) {
+            uint64_t const db = umma_desc_sw128(kb + (k >> 2) * HALF) + (uint64_t)((k & 3) * 2);
+            tc_mma_f16_ts(tmem_S + (uint32_t)(g & 1) * 128u, tmem_Q + (uint32_t)(k * 8), db, idesc_qk, k != 0);
+          }
+          tc_commit(&kv_empty[sb]);
+          tc_commit(&s_full[g & 1]);
+        };
+        SegWalk w;
+        w.init(sched);
+        int g0 = 0, seg = 0;
+        while (w.next(sched)) {
+          int const ntiles = w.t1 - w.t0;
+          if (g0 > 0) {
+            mbar_wait(&o_full, (g0 - 1) & 1); // every MMA of the previous segment has completed
+          }
+          FFB_TR(1, 4000 + seg);
+          mbar_wait(&q_full, seg & 1);        // Q of this segment is in tensor memory, O of the previous one was read out
+          tc_fence_after();
+          issue_qk(g0);
+          if (ntiles > 1) {
+            issue_qk(g0 + 1);
+          }
+          for (int it = 0; it < ntiles; it++) {
+            int const g = g0 + it;
+            int const j = 2 * g + 1, sb = j % NBUF;
+            mbar_wait(&p_full, g & 1);
+            FFB_TR(1, 2000 + g);
+            mbar_wait(&kv_full[sb], (j / NBUF) & 1);
+            FFB_TR(1, 3000 + g);
+            tc_fence_after();
+            uint32_t const vb = smem_u32(sKV + sb * Cfg::KV_BYTES);
+            uint32_t const tP = tmem_S + (uint32_t)(g & 1) * 128u;
 #pragma unroll
-            for (int v4 = 0; v4 < 4; v4++) {
-              float f[8];
-#pragma unroll
-              for (int e = 0; e < 8; e++) {
-                f[e] = __uint_as_float(r[v4 * 8 + e]) * inv;
-              }
-              dst[c * 4 + v4] = pack8<T>(f);
+            for (int k = 0; k < TBN / 16; k++) {
+              uint64_t const db = umma_desc_mn_sw128(vb + k * 2048, HALF, 1024);
+              tc_mma_f16_ts(tmem_O, tP + (uint32_t)(k * 8), db, idesc_pv, (it | k) != 0);
+            }
+            tc_commit(&kv_empty[sb]);
+            tc_commit(&o_full);
+            if (it + 2 < ntiles) {
+              mbar_wait(&o_full, g & 1); // P of this tile has been consumed: its score buffer may be overwritten
+              issue_qk(g + 2);
             }
           }
+          g0 += ntiles;
+          seg++;
         }
       }
     } else {
-      if (warp_active) {
-        float *rec = partial + ((size_t)(th >= 0 ? th : 0) * nsplit + split) * (DH + 2);
+      // ===== softmax warps: threads (row, h) with h = warp / 4 own keys [64h, 64h+64) of every tile =====
+      int const row = tid & (TBM - 1), hc = tid >> 7;
+      uint32_t const lane_sel = (uint32_t)((warp & 3) * 32) << 16;
+      uint32_t const pair_bar = 1 + (warp & 3); // named barrier shared by warps w and w+4
+      constexpr int OC = DH / 2;                // output columns per thread
+      constexpr int QW = DH / 4;                // 32-bit words of Q per thread (half a row)
+      uint32_t const tO = tmem_O + lane_sel + (uint32_t)(hc * OC);
+      uint32_t const tq = tmem_Q + lane_sel + (uint32_t)(hc * QW);
+
+      // Row data of a segment: fetched one segment ahead (global loads in flight during the tile loop), so a unit
+      // boundary costs no exposed global-memory latency.
+      int n_th = -1, n_kvl = 0, n_bit = -1;
+      unsigned long long n_mask = 0;
+      auto fetch_rows = [&](SegWalk const &sw) {
+        AtcEntry const &en = sched.ent[sw.e];
+        int const R = en.mt * TBM + row;
+        n_th = -1;
+        n_kvl = 0;
+        n_bit = -1;
+        if (R < en.qlen * G) {
+          int const tok = en.first_tok + R / G;
+          n_th = tok * nq + sw.kvh * G + R % G;
+          QueryDesc const qd = qdesc[tok];
+          n_kvl = qd.kv_len;
+          n_bit = qd.bit;
+        }
+        if (hc == 1 && row < 64) {
+          n_mask = meta->causalMask[en.slot].mask[row];
+        }
+      };
+      // Q -> tensor memory (all QK^T MMAs of the previous segment have completed: their s_full phases were observed),
+      // row tables -> shared-memory buffer `tb`
+      auto publish_rows = [&](int tb) {
+        uint32_t n_q[32];
+        uint4 const *src = reinterpret_cast<uint4 const *>(q_buf + (size_t)(n_th >= 0 ? n_th : 0) * DH + hc * (DH / 2));
 #pragma unroll
-        for (int c = 0; c < OC / 32; c++) {
-          uint32_t r[32];
-          tmem_ld32(tO + (uint32_t)(c * 32), r);
-          if (th >= 0) {
+        for (int c = 0; c < QW / 4; c++) { // q_buf was written by the prep kernel just before: L2 hits
+          uint4 const v = n_th >= 0 ? src[c] : make_uint4(0u, 0u, 0u, 0u);
+          n_q[c * 4 + 0] = v.x; n_q[c * 4 + 1] = v.y; n_q[c * 4 + 2] = v.z; n_q[c * 4 + 3] = v.w;
+        }
+        if (DH == 128) {
+          tmem_st32(tq, n_q);
+        } else {
+          tmem_st16(tq, n_q);
+        }
+        tmem_st_wait();
+        tc_fence_before();
+        mbar_arrive(&q_full);
+        if (hc == 1 && row < 64) {
+          s_mask[tb][row] = n_mask;
+        }
+      };
+
+      SegWalk w;
+      w.init(sched);
+      bool have = w.next(sched);
+      int g0 = 0, tb = 0;
+      if (have) {
+        fetch_rows(w);
+        publish_rows(0);
+      }
+      asm volatile("bar.sync 5, 256;" ::: "memory");
+      while (have) {
+        AtcEntry const &en = sched.ent[w.e];
+        int const ntiles = w.t1 - w.t0, ntcs = en.ntcs, t_first = w.t0;
+        // the pieces of this unit: CTAs whose ranges intersect its flattened tiles
+        int const U0 = en.cum + w.kvh * en.ntiles;
+        int const c_first = U0 / sched.rg, npieces = (U0 + en.ntiles - 1) / sched.rg - c_first + 1;
+        int const piece = (int)blockIdx.x - c_first;
+        int const th = n_th, kvl = n_kvl, bit = n_bit;
+        bool const warp_active = __any_sync(0xffffffffu, th >= 0); // padding-only warps just keep the barriers moving
+        have = w.next(sched);
+        if (have) {
+          fetch_rows(w); // next segment's rows: loads stay in flight while this segment streams
+        }
+        float m_ref = -INFINITY, l = 0.f;
+        // tree / beam rows: bit i of row_vis says whether tree position i (key ntcs + i) is visible to this row
+        // (mask rule tree_…cu:165-169 / spec_…cu:165-167 with 1ULL semantics), transposed once per segment
+        unsigned long long row_vis = 0;
+        if (__any_sync(0xffffffffu, bit >= 0 && bit < 64)) {
+          int const sb = bit & 63;
+#pragma unroll 8
+          for (int i = 0; i < 64; i++) {
+            row_vis |= ((s_mask[tb][i] >> sb) & 1ULL) << i;
+          }
+          if (bit < 0 || bit >= 64) {
+            row_vis = 0;
+          }
+        }
+
+        for (int it = 0; it < ntiles; it++) {
+          int const g = g0 + it, b = g & 1;
+          int const kbase = (t_first + it) * TBN + hc * 64; // first key of this thread's 64 columns
+          uint32_t const tS = tmem_S + (uint32_t)b * 128u + lane_sel;
+          bool const need_mask = __any_sync(0xffffffffu, th >= 0 && (kbase + 64 > kvl || (bit >= 0 && kbase + 64 > ntcs)));
+          float sc[64];
+          if (tid == 0) FFB_TR(2, 1000 + g);
+          mbar_wait(&s_full[b], (g >> 1) & 1);
+          if (tid == 0) FFB_TR(2, 2000 + g);
+          tc_fence_after();
+          float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+          if (warp_active) {
+            uint32_t r0[32], r1[32];
+            tmem_ld32_nowait(tS + (uint32_t)(hc * 64), r0);
+            tmem_ld32_nowait(tS + (uint32_t)(hc * 64 + 32), r1);
+            tmem_ld_wait();
 #pragma unroll
-            for (int e = 0; e < 32; e += 2) {
-              *reinterpret_cast<float2 *>(rec + hc * OC + c * 32 + e) = make_float2(__uint_as_float(r[e]), __uint_as_float(r[e + 1]));
+            for (int e = 0; e < 32; e++) { // raw scores; the (positive) scale is folded into the exponent below
+              sc[e] = __uint_as_float(r0[e]);
+              sc[32 + e] = __uint_as_float(r1[e]);
+            }
+            if (need_mask) {
+              // visibility of this thread's 64 keys as one 64-bit word: kv_len / causal bound, then the tree bits
+              int const lim = kvl - kbase;
+              unsigned long long V = lim >= 64 ? ~0ULL : (lim <= 0 ? 0ULL : ((1ULL << lim) - 1ULL));
+              if (bit >= 0) {
+                int const off = kbase - ntcs; // tree position of column 0
+                unsigned long long tv;
+                if (off >= 64) {
+                  tv = 0ULL;
+                } else if (off >= 0) {
+                  tv = row_vis >> off;
+                } else if (off > -64) {
+                  tv = (row_vis << (-off)) | ((1ULL << (-off)) - 1ULL);
+                } else {
+                  tv = ~0ULL;
+                }
+                V &= tv;
+              }
+              uint32_t const vlo = (uint32_t)V, vhi = (uint32_t)(V >> 32);
+#pragma unroll
+              for (int e = 0; e < 32; e++) {
+                sc[e] = (vlo >> e) & 1u ? sc[e] : -INFINITY;
+                sc[32 + e] = (vhi >> e) & 1u ? sc[32 + e] : -INFINITY;
+              }
+            }
+#pragma unroll
+            for (int e = 0; e < 64; e += 4) {
+              mx0 = fmaxf(mx0, sc[e]);
+              mx1 = fmaxf(mx1, sc[e + 1]);
+              mx2 = fmaxf(mx2, sc[e + 2]);
+              mx3 = fmaxf(mx3, sc[e + 3]);
             }
           }
+          float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * scale_log2; // log2 domain from here on
+          s_xch[b][hc][row] = mx;
+          asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+          mx = fmaxf(mx, s_xch[b][hc ^ 1][row]);
+          // lazy reference maximum: move it (and rescale the accumulator) only when the row maximum outgrows it by 2^8
+          bool const grow = mx > m_ref + kRescaleThreshold || (m_ref == -INFINITY && mx > -INFINITY);
+          float const alpha = grow ? (m_ref == -INFINITY ? 1.f : ffb_ex2(m_ref - mx)) : 1.f;
+          if (grow) {
+            m_ref = mx;
+          }
+          float const base = m_ref == -INFINITY ? 0.f : m_ref;
+          if (it > 0 && __any_sync(0xffffffffu, alpha != 1.f)) {
+            // rescale the accumulator rows whose reference moved; needs the PV MMA of the previous tile to be complete
+            // (the MMA of this tile cannot start before this thread arrives on p_full)
+            mbar_wait(&o_full, (g - 1) & 1);
+            tc_fence_after();
+#pragma unroll
+            for (int c = 0; c < OC / 32; c++) {
+              uint32_t r[32];
+              tmem_ld32(tO + (uint32_t)(c * 32), r);
+#pragma unroll
+              for (int e = 0; e < 32; e++) {
+                r[e] = __float_as_uint(__uint_as_float(r[e]) * alpha);
+              }
+              tmem_st32(tO + (uint32_t)(c * 32), r);
+            }
+            tmem_st_wait();
+          }
+          if (warp_active) {
+            // P (16-bit pairs) overwrites the first 64 columns of this tile's score buffer: this thread's 64 keys are
+            // columns [32h, 32h+32); the partner finished reading its scores before the pair barrier above
+            float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+            uint32_t pk[32];
+#pragma unroll
+            for (int e = 0; e < 64; e += 4) {
+              float f0 = fmaf(sc[e], scale_log2, -base), f1 = fmaf(sc[e + 1], scale_log2, -base);
+              float f2 = fmaf(sc[e + 2], scale_log2, -base), f3 = fmaf(sc[e + 3], scale_log2, -base);
+              f0 = ffb_ex2(f0);
+              f1 = ffb_ex2(f1);
+              f2 = ffb_ex2(f2);
+              f3 = ffb_ex2(f3);
+              s0 += f0;
+              s1 += f1;
+              s2 += f2;
+              s3 += f3;
+              pk[e / 2] = DT<T>::pack(f0, f1);
+              pk[e / 2 + 1] = DT<T>::pack(f2, f3);
+            }
+            l = l * alpha + ((s0 + s1) + (s2 + s3));
+            tmem_st32(tS + (uint32_t)(hc * 32), pk);
+            tmem_st_wait();
+          }
+          if (g > 0) {
+            // Phase bookkeeping: every thread observes every o_full phase in order, and cannot arrive on p_full for
+            // tile g before the p_full phase of tile g-1 has completed (PV(g-1) is issued only after it).
+            mbar_wait(&o_full, (g - 1) & 1);
+          }
+          if (tid == 0) FFB_TR(2, 3000 + g);
+          tc_fence_before();
+          mbar_arrive(&p_full); // this thread's part of P (and of the corrected O) is in place
         }
-        if (th >= 0 && hc == 0) {
-          rec[DH] = m_ref;
-          rec[DH + 1] = l;
+        // The next segment's Q goes to tensor memory BEFORE this segment's epilogue, so its first QK^T MMAs run
+        // while the output of this one is read out (its first PV MMA waits for these threads' p_full anyway).
+        if (have) {
+          publish_rows(tb ^ 1);
         }
-      }
-      if (fuse_combine) {
-        // per-row arrival counters: the last split to finish a (token, head) row merges its records
-        __threadfence();
-        asm volatile("bar.sync 5, 256;" ::: "memory");
-        if (hc == 0) {
-          int last = 0;
-          if (th >= 0 && k0 < kvl) {
-            int const nvalid = min(nsplit, (kvl + chunk - 1) / chunk);
-            int const prev = atomicAdd(&split_counter[th], 1);
-            last = prev == nvalid - 1;
-            if (last) {
-              split_counter[th] = 0;
+        // ---- segment epilogue: row sum over both column halves, then output or split record ----
+        int const g_last = g0 + ntiles - 1;
+        if (tid == 0) FFB_TR(2, 4000);
+        s_xch[0][hc][row] = l;
+        mbar_wait(&o_full, g_last & 1);
+        tc_fence_after();
+        asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+        l += s_xch[0][hc ^ 1][row];
+        if (npieces == 1) {
+          if (warp_active) {
+            float const inv = __fdividef(1.f, l + 1.e-6f);
+            uint4 *dst = reinterpret_cast<uint4 *>(out + (size_t)(th >= 0 ? th : 0) * DH + hc * OC);
+#pragma unroll
+            for (int c = 0; c < OC / 32; c++) {
+              uint32_t r[32];
+              tmem_ld32(tO + (uint32_t)(c * 32), r);
+              if (th >= 0) {
+#pragma unroll
+                for (int v4 = 0; v4 < 4; v4++) {
+                  float f[8];
+#pragma unroll
+                  for (int e = 0; e < 8; e++) {
+                    f[e] = __uint_as_float(r[v4 * 8 + e]) * inv;
+                  }
+                  dst[c * 4 + v4] = pack8<T>(f);
+                }
+              }
             }
           }
-          s_rowlast[row] = last;
-        }
-        asm volatile("bar.sync 5, 256;" ::: "memory");
-        __threadfence();
-        for (int r = warp; r < TBM; r += 8) {
-          if (s_rowlast[r]) {
-            int const t2 = s_tok[r];
-            int const nvalid = min(nsplit, (s_kvlen[r] + chunk - 1) / chunk);
-            combine_record<T, DH>(partial + (size_t)t2 * nsplit * (DH + 2), nvalid, out + (size_t)t2 * DH, lane, 32);
+        } else {
+          // Split records live in per-CTA slots laid out [DH + 2][128 rows] (column-major over the rows), so that a
+          // warp - one row per lane - writes and later reads 128 contiguous bytes per instruction.  Piece i of a
+          // unit is held by CTA c_first + i: slot 2c + 1 when the unit runs past that CTA's range (its last
+          // segment), slot 2c when the unit ends there (its first segment).
+          constexpr int SLOT = (DH + 2) * TBM;
+          if (tid == 0) FFB_TR(2, 4050);
+          if (warp_active) {
+            float *rec = partial + (size_t)(2 * (int)blockIdx.x + (piece < npieces - 1 ? 1 : 0)) * SLOT + row;
+#pragma unroll
+            for (int c = 0; c < OC / 32; c++) {
+              uint32_t r[32];
+              tmem_ld32(tO + (uint32_t)(c * 32), r);
+#pragma unroll
+              for (int e = 0; e < 32; e++) {
+                rec[(hc * OC + c * 32 + e) * TBM] = __uint_as_float(r[e]);
+              }
+            }
+            if (hc == 0) {
+              rec[DH * TBM] = m_ref;
+              rec[(DH + 1) * TBM] = l;
+            }
+          }
+          // per-row arrival counters: the last piece to finish a (token, head) row merges the records; both threads
+          // of the row merge their own half of the columns (exact log-sum-exp merge, then the reference's
+          // 1/(sum + 1e-6), inc_…cu:538)
+          if (tid == 0) FFB_TR(2, 4100);
+          __threadfence();
+          if (tid == 0) FFB_TR(2, 4200);
+          asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+          if (hc == 0) {
+            int last = 0;
+            if (th >= 0) {
+              int const prev = atomicAdd(&split_counter[th], 1);
+              last = prev == npieces - 1;
+              if (last) {
+                split_counter[th] = 0;
+              }
+            }
+            s_rowlast[row] = last;
+          }
+          asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+          if (tid == 0) FFB_TR(2, 4300 + s_rowlast[row]);
+          if (s_rowlast[row]) {
+            __threadfence();
+            float const *rec0 = partial + row;
+            auto slot_of = [&](int i) { return rec0 + (size_t)(2 * (c_first + i) + (i < npieces - 1 ? 1 : 0)) * SLOT; };
+            float M = -INFINITY, L = 0.f;
+            for (int i = 0; i < npieces; i++) {
+              M = fmaxf(M, __ldcg(slot_of(i) + DH * TBM));
+            }
+            for (int i = 0; i < npieces; i++) {
+              float const mi = __ldcg(slot_of(i) + DH * TBM);
+              L += __ldcg(slot_of(i) + (DH + 1) * TBM) * (mi == -INFINITY ? 0.f : ffb_ex2(mi - M));
+            }
+            float const inv = __fdividef(1.f, L + 1.e-6f);
+            uint4 *dst = reinterpret_cast<uint4 *>(out + (size_t)th * DH + hc * OC);
+            // 32 columns x 2 pieces per batch: 64 independent loads in flight per thread
+#pragma unroll 1
+            for (int c = 0; c < OC / 32; c++) {
+              float acc[32];
+#pragma unroll
+              for (int d = 0; d < 32; d++) {
+                acc[d] = 0.f;
+              }
+#pragma unroll 1
+              for (int i = 0; i < npieces; i += 2) {
+                bool const two = i + 1 < npieces;
+                float const *ra = slot_of(i), *rb = slot_of(two ? i + 1 : i);
+                float const ma = __ldcg(ra + DH * TBM), mb = __ldcg(rb + DH * TBM);
+                float va[32], vb[32];
+#pragma unroll
+                for (int d = 0; d < 32; d++) {
+                  va[d] = __ldcg(ra + (hc * OC + c * 32 + d) * TBM);
+                  vb[d] = __ldcg(rb + (hc * OC + c * 32 + d) * TBM);
+                }
+                float const wa = ma == -INFINITY ? 0.f : ffb_ex2(ma - M);
+                float const wb = (!two || mb == -INFINITY) ? 0.f : ffb_ex2(mb - M);
+#pragma unroll
+                for (int d = 0; d < 32; d++) {
+                  acc[d] = fmaf(va[d], wa, fmaf(vb[d], wb, acc[d]));
+                }
+              }
+#pragma unroll
+              for (int v4 = 0; v4 < 4; v4++) {
+                float f[8];
+#pragma unroll
+                for (int e = 0; e < 8; e++) {
+                  f[e] = acc[v4 * 8 + e] * inv;
+                }
+                dst[c * 4 + v4] = pack8<T>(f);
+              }
+            }
+            if (tid == 0) FFB_TR(2, 4400);
           }
         }
+        if (tid == 0) FFB_TR(2, 5000);
+        asm volatile("bar.sync 5, 256;" ::: "memory"); // next segment's tables are published, this one's are free
+        tb ^= 1;
+        g0 += ntiles;
       }
+      tc_fence_before();
     }
-    tc_fence_before();
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 8) {
+  if (warp == 9) {
     tc_fence_after();
     __syncwarp();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u));
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base_smem), "r"(512u));
   }
 }
 
 } // namespace
-
-// Split choice: CTAs are (request, kv head, row tile, split); one CTA per SM is resident, so pick the chunk
-// (a multiple of the 128-key tile) that minimises waves x tiles-per-CTA plus a per-CTA fixed cost.
-static int choose_tc_chunk(long units, int kv_len_max, int *nsplit_out) {
-  if (char const *e = getenv("FFB_ATTN_TC_CHUNK")) {
-    int v = atoi(e);
-    if (v > 0) {
-      v = ((v + TBN - 1) / TBN) * TBN;
-      *nsplit_out = (kv_len_max + v - 1) / v;
-      return v;
-    }
-  }
-  int const tiles_total = (kv_len_max + TBN - 1) / TBN;
-  double best = 1e30;
-  int best_ns = 1, best_chunk = tiles_total * TBN;
-  for (int ns = 1; ns <= 16 && ns <= tiles_total; ns++) {
-    int const tpc = (tiles_total + ns - 1) / ns; // tiles per chunk
-    int const real_ns = (tiles_total + tpc - 1) / tpc;
-    if (real_ns != ns) {
-      continue;
-    }
-    long const ctas = units * ns;
-    long const waves = (ctas + kNumSMs - 1) / kNumSMs;
-    double const cost = (double)waves * (tpc + 1.5) + (ns > 1 ? 0.5 : 0.0);
-    if (cost < best - 1e-9) {
-      best = cost;
-      best_ns = ns;
-      best_chunk = tpc * TBN;
-    }
-  }
-  *nsplit_out = best_ns;
-  return best_chunk;
-}
 
 int attn_tc_supported(ffb_attn_s *h) {
   return h->tm_ready && !getenv("FFB_DISABLE_ATTN_TC");
@@ -480,26 +622,106 @@ int attn_tc_init(ffb_attn_s *h) {
   return FFB_OK;
 }
 
-int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, void *out, int T, int kv_len_max,
-                   int q_len_max, cudaStream_t s) {
+// Returns FFB_OK when launched, an FFB_ERR_* code on failure, or -1 when the batch does not fit the schedule
+// table (the caller then uses the mma.sync kernel).
+int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, void *out, int T, AtcReq const *reqs,
+                   int nreq, cudaStream_t s) {
   ffb_attn_desc const &d = h->d;
-  if (T <= 0) {
+  if (T <= 0 || nreq <= 0) {
     return FFB_OK;
   }
   int const G = d.num_q_heads / d.num_kv_heads;
-  int const m_tiles = (q_len_max * G + TBM - 1) / TBM;
-  long const units = (long)((T + q_len_max - 1) / (q_len_max > 0 ? q_len_max : 1)) * d.num_kv_heads * m_tiles;
-  int nsplit = 1;
-  int chunk = choose_tc_chunk(units, kv_len_max < 1 ? 1 : kv_len_max, &nsplit);
-  size_t const rec = (size_t)(d.head_dim + 2) * sizeof(float);
-  while (nsplit > 1 && (size_t)T * d.num_q_heads * nsplit * rec > h->partial_bytes) {
-    chunk *= 2;
-    nsplit = (kv_len_max + chunk - 1) / chunk;
+  AtcSched sc;
+  sc.n_ent = 0;
+  int cum = 0;
+  for (int i = 0; i < nreq; i++) {
+    AtcReq const &rq = reqs[i];
+    if (rq.qlen <= 0) {
+      continue;
+    }
+    int const m_tiles = (rq.qlen * G + TBM - 1) / TBM;
+    for (int mt = 0; mt < m_tiles; mt++) {
+      if (sc.n_ent == ATC_MAX_ENT) {
+        return -1;
+      }
+      int const qi_last = std::min(rq.qlen - 1, (mt * TBM + TBM - 1) / G);
+      int kv_hi = rq.causal ? std::min(rq.tl, rq.first_depth + qi_last + 1) : rq.tl; // attn_prep.cu kv_len rules
+      kv_hi = std::max(1, std::min(kv_hi, h->cache_len));
+      int const ntiles = (kv_hi + TBN - 1) / TBN;
+      if (ntiles > 32767 || rq.qlen > 32767) {
+        return -1;
+      }
+      AtcEntry &e = sc.ent[sc.n_ent++];
+      e.cum = cum;
+      e.first_tok = rq.first_tok;
+      e.ntcs = rq.ntcs;
+      e.slot = (short)rq.slot;
+      e.mt = (short)mt;
+      e.ntiles = (short)ntiles;
+      e.qlen = (short)rq.qlen;
+      cum += d.num_kv_heads * ntiles;
+    }
   }
+  if (sc.n_ent == 0) {
+    return FFB_OK;
+  }
+  sc.total = cum;
+  // Tiles per CTA.  rg0 = ceil(total / SMs) balances perfectly but cuts units at almost every CTA boundary, and a
+  // cut costs a split record + merge (~4 tiles of time); a slightly longer range whose boundaries fall on unit
+  // boundaries can be cheaper.  Cost model: rg + 4 * (most partial segments any CTA has), rg in [rg0, 2 rg0].
+  int const rg0 = (cum + kNumSMs - 1) / kNumSMs;
+  auto max_partials = [&](int rgc) {
+    int e = 0, worst = 0, prev_cut = 0;
+    for (int x = rgc; x < cum + rgc; x += rgc) { // x: end of a CTA range (the last one is clipped to total)
+      int cut = 0;
+      if (x < cum) {
+        while (e + 1 < sc.n_ent && sc.ent[e + 1].cum <= x) {
+          e++;
+        }
+        cut = ((x - sc.ent[e].cum) % sc.ent[e].ntiles) != 0;
+      }
+      worst = std::max(worst, prev_cut + cut);
+      prev_cut = cut;
+    }
+    return worst;
+  };
+  int rg = rg0, best_cost = 1 << 30;
+  for (int rgc = rg0; rgc <= 2 * rg0; rgc++) {
+    int const cost = rgc + 4 * max_partials(rgc);
+    if (cost < best_cost) {
+      best_cost = cost;
+      rg = rgc;
+    }
+  }
+  if (char const *e = getenv("FFB_ATC_RG")) {
+    int v = atoi(e);
+    if (v > 0) {
+      rg = v;
+    }
+  }
+  // split records: two slots of [Dh + 2][128] floats per CTA (see the kernel's epilogue)
+  size_t const slot_bytes = (size_t)(d.head_dim + 2) * TBM * sizeof(float);
+  while ((size_t)2 * ((cum + rg - 1) / rg) * slot_bytes > h->partial_bytes) {
+    rg *= 2; // fewer, longer CTA ranges
+  }
+  int maxp = 1;
+  for (int i = 0; i < sc.n_ent; i++) {
+    maxp = std::max(maxp, (sc.ent[i].ntiles - 1 + rg - 1) / rg + 1);
+  }
+  sc.rg = rg;
+  sc.maxpieces = maxp;
+  int const grid = (cum + rg - 1) / rg;
   float const scale = d.qk_prod_scaling ? 1.0f / sqrtf((float)d.head_dim) : 1.0f;
   float const scale_log2 = scale * 1.4426950408889634f;
-  int const fuse = getenv("FFB_SEPARATE_COMBINE") ? 0 : 1;
-  dim3 grid(nsplit, d.num_kv_heads * m_tiles, d.max_requests);
+  static long long *trace = nullptr;
+  static int trace_calls = 0;
+  bool const tracing = getenv("FFB_ATC_TRACE") != nullptr;
+  if (tracing && !trace) {
+    cudaMalloc(&trace, 3 * 512 * sizeof(long long));
+  }
+  if (tracing) {
+    cudaMemsetAsync(trace, 0, 3 * 512 * sizeof(long long), s);
+  }
   CUtensorMap const &tmK = *reinterpret_cast<CUtensorMap const *>(h->tmK);
   CUtensorMap const &tmV = *reinterpret_cast<CUtensorMap const *>(h->tmV);
   if (h->profiling) {
@@ -513,10 +735,9 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
       FFB_CUDA_TRY(cudaFuncSetAttribute(attn_tc_kernel<TT, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
       attr_set = true;                                                                                               \
     }                                                                                                                \
-    attn_tc_kernel<TT, DH><<<grid, ATC_THREADS, smem, s>>>(                                                          \
-        tmK, tmV, (TT const *)h->q_buf, h->qdesc, meta, h->partial, h->split_counter, (TT *)out, d.mode,             \
-        d.num_q_heads, d.num_kv_heads, h->cache_len, m_tiles, chunk, nsplit, scale_log2,                             \
-        h->num_generation_tokens_cur, fuse);                                                                         \
+    attn_tc_kernel<TT, DH><<<grid, ATC_THREADS, smem, s>>>(tmK, tmV, sc, (TT const *)h->q_buf, h->qdesc, meta,       \
+                                                            h->partial, h->split_counter, (TT *)out, d.num_q_heads,   \
+                                                            d.num_kv_heads, h->cache_len, scale_log2, tracing ? trace : nullptr); \
   } while (0)
   if (d.dtype == FFB_DT_HALF) {
     if (d.head_dim == 128) FFB_ATC(__half, 128); else FFB_ATC(__half, 64);
@@ -528,8 +749,17 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
     cudaEventRecord(h->ev1, s);
   }
   FFB_LAUNCH_CHECK();
-  if (nsplit > 1 && !fuse) {
-    return launch_combine(h, out, T, chunk, nsplit, s);
+  if (tracing && ++trace_calls == atoi(getenv("FFB_ATC_TRACE"))) { // dump the n-th launch
+    static long long host[3 * 512];
+    cudaStreamSynchronize(s);
+    cudaMemcpy(host, trace, sizeof(host), cudaMemcpyDeviceToHost);
+    long long t0 = host[1];
+    for (int r = 0; r < 3; r++) {
+      for (int i = 0; i < 255 && host[r * 512 + 2 * i + 1]; i++) {
+        fprintf(stderr, "TRACE role %d ev %lld t %lld\n", r, host[r * 512 + 2 * i], host[r * 512 + 2 * i + 1] - t0);
+      }
+    }
+    fprintf(stderr, "TRACE grid %d rg %d maxp %d total %d\n", grid, rg, maxp, cum);
   }
   return FFB_OK;
 }

@@ -47,11 +47,14 @@ int ffb_check_device(void) {
 // Multi-query attention: the tcgen05 / TMA kernel (attn_tc.cu) by default; FFB_ATTN_TC=0 selects the mma.sync
 // kernel (attn_multi.cu), kept as the in-tree comparison point.
 static int launch_multi_dispatch(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, void *out, int T,
-                                 int kv_len_max, int q_len_max, cudaStream_t s) {
+                                 int kv_len_max, int q_len_max, AtcReq const *reqs, int nreq, cudaStream_t s) {
   char const *e = getenv("FFB_ATTN_TC");
   bool const want_tc = !(e && e[0] == '0');
   if (want_tc && attn_tc_supported(h)) {
-    return launch_attn_tc(h, meta, out, T, kv_len_max, q_len_max, s);
+    int const rc = launch_attn_tc(h, meta, out, T, reqs, nreq, s);
+    if (rc != -1) {
+      return rc;
+    } // -1: the batch does not fit the schedule table
   }
   return launch_multi_attn(h, meta, out, T, kv_len_max, q_len_max, s);
 }
@@ -96,6 +99,11 @@ int ffb_attn_create(ffb_attn_desc const *desc, ffb_attn_t *out) {
   size_t const part_min = (size_t)d.num_q_heads * ((h->cache_len + 63) / 64) * rec * 2;
   if (part > ((size_t)96 << 20)) {
     part = (size_t)96 << 20;
+  }
+  // the tcgen05 multi-query kernel keeps two split-record slots of [Dh + 2][128] floats per CTA (attn_tc.cu)
+  size_t const part_tc = (size_t)2 * kNumSMs * (d.head_dim + 2) * 128 * sizeof(float);
+  if (part < part_tc) {
+    part = part_tc;
   }
   if (part < part_min) {
     part = part_min;
@@ -205,6 +213,13 @@ namespace {
 struct BatchScan {
   int kv_len_max = 0, q_len_max = 0;
   bool any_multi = false; // some request contributes more than one query row per head
+  int nreq = 0;
+  AtcReq reqs[FFB_MAX_NUM_REQUESTS];
+  void add(int slot, ffb_per_request_info const &ri, int qlen, int tl, int ntcs, bool causal) {
+    AtcReq &r = reqs[nreq++];
+    r.slot = slot; r.first_tok = ri.first_token_offset_in_batch; r.qlen = qlen; r.tl = tl; r.ntcs = ntcs;
+    r.causal = causal ? 1 : 0; r.first_depth = ri.first_token_depth_in_request;
+  }
 };
 
 int check_common(ffb_attn_t h, ffb_batch_config const *bc, void const *meta, void const *qkv, void *out, int mode) {
@@ -256,6 +271,7 @@ int ffb_inc_attn_forward(ffb_attn_t h, ffb_batch_config const *bc, ffb_combined_
     sc.kv_len_max = tl > sc.kv_len_max ? tl : sc.kv_len_max;
     sc.q_len_max = ri.num_tokens_in_batch > sc.q_len_max ? ri.num_tokens_in_batch : sc.q_len_max;
     sc.any_multi |= ri.num_tokens_in_batch > 1;
+    sc.add(i, ri, ri.num_tokens_in_batch, tl, bc->causalMask[i].non_tree_cache_size, ri.prompt_phase);
   }
   h->num_generation_tokens_cur = bc->num_generation_tokens;
   rc = launch_prep(h, FFB_INC_DECODING_MODE, meta, qkv, T, bc->num_generation_tokens, 0, s);
@@ -265,7 +281,7 @@ int ffb_inc_attn_forward(ffb_attn_t h, ffb_batch_config const *bc, ffb_combined_
   int const force = forced_kernel();
   bool const use_decode = force == 1 || (force == 0 && !sc.any_multi && h->G == 1);
   return use_decode ? launch_decode_attn(h, meta, out, T, sc.kv_len_max, s)
-                    : launch_multi_dispatch(h, meta, out, T, sc.kv_len_max, sc.q_len_max, s);
+                    : launch_multi_dispatch(h, meta, out, T, sc.kv_len_max, sc.q_len_max, sc.reqs, sc.nreq, s);
 }
 
 int ffb_tree_attn_forward(ffb_attn_t h, ffb_tree_verify_batch_config const *tbc,
@@ -309,13 +325,14 @@ int ffb_tree_attn_forward(ffb_attn_t h, ffb_tree_verify_batch_config const *tbc,
     FFB_REQUIRE(tl <= h->cache_len, "request %d: %d tokens exceed the cache length %d", i, tl, h->cache_len);
     sc.kv_len_max = tl > sc.kv_len_max ? tl : sc.kv_len_max;
     sc.q_len_max = ri.num_tokens_in_batch > sc.q_len_max ? ri.num_tokens_in_batch : sc.q_len_max;
+    sc.add(i, ri, ri.num_tokens_in_batch, tl, bc->causalMask[i].non_tree_cache_size, ri.prompt_phase);
   }
   h->num_generation_tokens_cur = bc->num_generation_tokens;
   rc = launch_prep(h, FFB_TREE_VERIFY_MODE, meta, qkv, T, bc->num_generation_tokens, 0, s);
   if (rc != FFB_OK) {
     return rc;
   }
-  return launch_multi_dispatch(h, meta, out, T, sc.kv_len_max, sc.q_len_max, s);
+  return launch_multi_dispatch(h, meta, out, T, sc.kv_len_max, sc.q_len_max, sc.reqs, sc.nreq, s);
 }
 
 int ffb_spec_attn_forward(ffb_attn_t h, ffb_beam_search_batch_config const *bbc,
@@ -346,13 +363,14 @@ int ffb_spec_attn_forward(ffb_attn_t h, ffb_beam_search_batch_config const *bbc,
     FFB_REQUIRE(tl <= h->cache_len, "request %d: %d tokens exceed the cache length %d", i, tl, h->cache_len);
     sc.kv_len_max = tl > sc.kv_len_max ? tl : sc.kv_len_max;
     sc.q_len_max = ql > sc.q_len_max ? ql : sc.q_len_max;
+    sc.add(i, ri, ql, tl, bm.non_tree_cache_size, !speculative);
   }
   h->num_generation_tokens_cur = bc->num_generation_tokens;
   rc = launch_prep(h, FFB_BEAM_SEARCH_MODE, meta, qkv, T, bc->num_generation_tokens, bbc->speculative_request_num, s);
   if (rc != FFB_OK) {
     return rc;
   }
-  return launch_multi_dispatch(h, meta, out, T, sc.kv_len_max, sc.q_len_max, s);
+  return launch_multi_dispatch(h, meta, out, T, sc.kv_len_max, sc.q_len_max, sc.reqs, sc.nreq, s);
 }
 
 int ffb_attn_read_kv(ffb_attn_t h, int request, int pos0, int n, void *k, void *v, ffb_stream_t stream) {

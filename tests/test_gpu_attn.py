@@ -122,6 +122,31 @@ def test_tree_verify_64_nodes_wide_mask():
     assert TL.rel_err(got, want) < TOL
 
 
+@pytest.mark.parametrize("tc", ["1", "0"])
+@pytest.mark.parametrize("dt,nq,nkv,dh", [("half", 32, 8, 128), ("bf16", 16, 16, 64)])
+def test_tree_verify_ragged_stream_k(dt, nq, nkv, dh, tc, monkeypatch):
+    """Ragged request lengths x many heads: the tcgen05 kernel's stream-K schedule cuts units into 3+ pieces
+    (split records + last-arriver merge), several row tiles per request (GQA), a prompt chunk in the same batch.
+    tc=0 runs the same batch through the mma.sync kernel."""
+    monkeypatch.setenv("FFB_ATTN_TC", tc)
+    rng = np.random.default_rng(21)
+    p = _pair(B.TREE_VERIFY_MODE, dt, nq, nkv, dh, 8, 3100, 512)
+    lens = {0: 3000, 1: 50, 3: 700, 4: 1500, 6: 129, 7: 2047}
+    reqs = []
+    for i, (s, n) in enumerate(lens.items()):
+        p.fill_cache(rng, s, n)
+        reqs.append(dict(slot=s, committed_len=n, parent=TL.random_tree(rng, 16 + 9 * i)))
+    reqs.insert(2, dict(slot=2, first_depth=0, ntok=150, prompt=True))
+    bc = TL.make_tree_batch(reqs)
+    qkv = _qkv(rng, bc.num_tokens, nq, nkv, dh, dt)
+    got, want = p.forward_both(bc, qkv)
+    assert np.isfinite(got).all()
+    assert TL.rel_err(got, want) < TOL
+    # per-token check: no row may be off (a lost or doubly counted split piece would hit single rows)
+    per_tok = np.abs(got - want).reshape(bc.num_tokens, -1).max(axis=1) / max(1e-6, np.abs(want).max())
+    assert per_tok.max() < 2e-2, (int(per_tok.argmax()), float(per_tok.max()))
+
+
 def test_tree_commit_state_error():
     from flexflow_b200.lib import FFBError
     rng = np.random.default_rng(15)

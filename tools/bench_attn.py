@@ -76,12 +76,13 @@ def main():
 
     def tree7b(ntree):
         def f():
-            lens = {s: 1024 for s in range(8)}
-            return TL.make_tree_batch([dict(slot=s, committed_len=1024, parent=TL.random_tree(rng, ntree)) for s in range(8)]), lens
+            ctx = int(os.environ.get("FFB_BENCH_CTX", "1024"))
+            lens = {s: ctx for s in range(8)}
+            return TL.make_tree_batch([dict(slot=s, committed_len=ctx, parent=TL.random_tree(rng, ntree)) for s in range(8)]), lens
         return f
     if only != "cfg4" or True:
         pass
-    res.append(run("cfg4 7B tree-verify b8 x64 ctx1024", B.TREE_VERIFY_MODE, 32, 32, 128, tree7b(64), 8, 1100, 512))
+    res.append(run("cfg4 7B tree-verify b8 x64 ctx1024", B.TREE_VERIFY_MODE, 32, 32, 128, tree7b(64), 8, int(os.environ.get("FFB_BENCH_CTX", "1024")) + 76, 512))
     if only == "cfg4":
         return
     res.append(run("cfg4' 7B tree-verify b8 x25 ctx1024 (reference max tree)", B.TREE_VERIFY_MODE, 32, 32, 128, tree7b(25), 8, 1100, 512))
