@@ -138,7 +138,8 @@ def run_ours(args):
     for lyr in model.layers:
         if lyr.op_type == "linear":
             in_dim, out_dim = lyr.inputs[0].dim, lyr.output.dim
-            std = (1.0 / in_dim) ** 0.5 * (8.0 if lyr.name.endswith("o_proj") else 1.0)
+            # fan-in of the UNSHARDED layer, so the all-reduced o_proj output has the same scale at every TP degree
+            std = (1.0 / HIDDEN) ** 0.5 * (8.0 if lyr.name.endswith("o_proj") else 1.0)
             lyr.weight = (torch.randn(out_dim, in_dim, generator=g, device=dev, dtype=torch.float32) * std).half()
         elif lyr.op_type == "inc_attn":
             attn_metas.append(lyr.meta)
@@ -251,6 +252,11 @@ def run_ours(args):
                      "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg,
                      "attn_share_of_step": k_ms * LAYERS / ms_dev},
     }
+    if not args.no_tree_verify:
+        try:
+            line["tree_verify"] = tree_verify_extra(args, dev, comm, rank, tp, model, g)
+        except Exception as e:  # the headline line must still print
+            line["tree_verify"] = {"error": repr(e)}
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(max_seconds=25.0)
@@ -258,6 +264,123 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def tree_verify_extra(args, dev, comm, rank, tp, decode_model, g):
+    """BASELINE.json configs[3] shapes (LLaMA-2-7B LLM, 8 requests x 64 tree tokens, 1024 committed tokens) through
+    the same hot path: qkv_proj (tcgen05 GEMM, M=512) -> TreeIncMultiHeadSelfAttention -> o_proj, 32 layers.
+    Reported beside the headline decode line: step time, the tcgen05 attention kernel's algorithmic HBM rate and
+    the projection GEMMs' tensor throughput (per-op CUDA-event timing, eager launches)."""
+    import numpy as np
+    import torch
+
+    import ffb_testlib as TL
+    from flexflow_b200 import ops
+    from flexflow_b200.model import FFConfig, FFModel
+
+    NREQ, NTREE, COMMITTED = 8, 64, 1024
+    T = NREQ * NTREE
+    nq_l, nkv_l = NQ // tp, max(1, NKV // tp)
+    H_l = nq_l * DH
+    cfg = FFConfig(data_type=torch.float16, tensor_parallelism_degree=tp, tp_rank=rank, max_requests_per_batch=NREQ,
+                   max_tokens_per_batch=T, max_sequence_length=COMMITTED + 16, max_spec_tree_token_num=NTREE, device=dev)
+    model = FFModel(cfg, comm)
+    t_in = model.create_tensor(HIDDEN)
+    t = t_in
+    rope = ops.RotaryEmbeddingMeta(apply_rotary_embedding=True, rope_theta=10000.0)
+    for i in range(LAYERS):
+        qkv = model.dense(t, 3 * H_l, name="layers.%d.self_attn.qkv_proj" % i)
+        a = model.inc_multiquery_self_attention_verify(qkv, HIDDEN, NQ, NKV, rotary_embedding_meta=rope,
+                                                       name="layers.%d.self_attn" % i)
+        t = model.dense(a, HIDDEN, name="layers.%d.self_attn.o_proj" % i)
+    model.compile_inference()
+    weights = {l.name: l.weight for l in decode_model.layers if l.op_type == "linear"}
+    kfill = torch.randn(COMMITTED, nkv_l, DH, generator=g, device=dev, dtype=torch.float16)
+    attn_metas = []
+    for lyr in model.layers:
+        if lyr.op_type == "linear":
+            lyr.weight = weights[lyr.name]  # same random-init weights as the decode model
+        elif lyr.op_type == "tree_attn":
+            attn_metas.append(lyr.meta)
+            for s in range(NREQ):
+                lyr.meta.write_kv(s, 0, kfill, kfill)
+    rng = np.random.default_rng(0)
+    bc = TL.make_tree_batch([dict(slot=s, committed_len=COMMITTED, parent=TL.random_tree(rng, NTREE)) for s in range(NREQ)])
+    hidden = torch.randn(T, HIDDEN, generator=g, device=dev, dtype=torch.float16)
+    model.handler.load_batch_config(bc)
+
+    def step():
+        return model.inference(bc, t_in, hidden, upload=False)
+    for _ in range(3):
+        out = step()
+    torch.cuda.synchronize()
+    if not torch.isfinite(out.float()).all():
+        bad = [(l.name, int((~torch.isfinite(l.output.buf[:T].float())).sum())) for l in model.layers
+               if not torch.isfinite(l.output.buf[:T].float()).all()]
+        raise AssertionError("non-finite tree-verify output; first bad layers: %s" % bad[:3])
+    graph = None
+    try:
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            out = step()
+        graph.replay()
+        torch.cuda.synchronize()
+    except Exception as e:
+        print("[bench] tree-verify graph capture failed (%s); timing eager launches" % e, file=sys.stderr)
+        graph = None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    steps = max(5, min(args.steps, 20))
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(steps):
+        graph.replay() if graph is not None else step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms_step = e0.elapsed_time(e1) / steps
+    # attention kernel (profiling events inside the C ABI) and per-op GEMM times, eager
+    for m in attn_metas:
+        m.set_profiling(True)
+    kms = []
+    for _ in range(3):
+        step()
+        torch.cuda.synchronize()
+        kms.extend(m.last_kernel_ms() for m in attn_metas)
+    for m in attn_metas:
+        m.set_profiling(False)
+    k_ms = sum(kms) / len(kms)
+    lin = {"qkv_proj": [], "o_proj": []}
+    x_in = torch.randn(T, HIDDEN, generator=g, device=dev, dtype=torch.float16)
+    x_attn = torch.randn(T, H_l, generator=g, device=dev, dtype=torch.float16)
+    for kind, x in (("qkv_proj", x_in), ("o_proj", x_attn)):
+        lyrs = [l for l in model.layers if l.op_type == "linear" and l.name.endswith(kind)]
+        for rep in range(3):  # 32 back-to-back launches per timing (weights rotate through 4.3 GB: no L2 reuse)
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            for lyr in lyrs:
+                ops.Linear.inference_kernel_wrapper(lyr.meta, bc, x, lyr.output.buf, lyr.weight, None, x.shape[1],
+                                                    lyr.output.dim, T)
+            a1.record()
+            torch.cuda.synchronize()
+            if rep:
+                lin[kind].append(a0.elapsed_time(a1) / len(lyrs))
+    elt = 2
+    kv = 2 * NREQ * (COMMITTED + NTREE) * nkv_l * DH * elt
+    alg = kv + T * (nq_l + 2 * nkv_l) * DH * elt + T * nq_l * DH * elt + 2 * T * nkv_l * DH * elt
+    peak, _ = peaks()
+    tf_peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("bf16_tflops", 1621.0) \
+        if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 1621.0
+    res = {"workload": "LLaMA-2-7B tree-verify, 8 requests x 64 tree tokens, 1024 committed tokens, tp%d" % tp,
+           "tokens_per_step": T, "ms_per_step": ms_step, "tree_tokens_per_s": T / (ms_step * 1e-3),
+           "attn_kernel": "attn_tc_kernel<half,128>", "attn_kernel_ms": k_ms, "attn_algorithmic_bytes": alg,
+           "attn_gbs": alg / (k_ms * 1e-3) / 1e9, "attn_frac_of_hbm_peak": alg / (k_ms * 1e-3) / 1e9 / peak,
+           "cuda_graph": graph is not None}
+    for kind, (K_, N_) in (("qkv_proj", (HIDDEN, 3 * H_l)), ("o_proj", (H_l, HIDDEN))):
+        ms = sorted(lin[kind])[len(lin[kind]) // 2]
+        tf = 2.0 * T * K_ * N_ / (ms * 1e-3) / 1e12
+        res[kind] = {"M": T, "K": K_, "N": N_, "ms": ms, "tflops": tf, "frac_of_measured_bf16_peak": tf / tf_peak}
+    for m in attn_metas:
+        m.close()
+    return res
 
 
 class CpuLayer:
@@ -344,6 +467,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-tree-verify", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -21,6 +21,7 @@ SOURCES = [
     "linear_stream.cu",
     "linear_gemv.cu",
     "linear_tc.cu",
+    "linear_tc2.cu",
     "capi_linear.cu",
     "comm.cu",
 ]

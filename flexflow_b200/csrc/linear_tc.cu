@@ -172,6 +172,10 @@ int make_tensor_map_2d(CUtensorMap *tm, int dtype, void const *ptr, long rows, i
 }
 
 
+int linear_tc2_supported(int dtype, int M, int K, int N);
+int launch_linear_tc2(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N,
+                      cudaStream_t s);
+
 struct LinearTcState {
   int dtype, quant, K, N, max_batch;
   void *scratch = nullptr; // dequantised weights [N][K] DT (quantised layers only)
@@ -223,6 +227,9 @@ int launch_linear_tc(LinearTcState *st, int dtype, int quant, void const *in, vo
       return rc;
     }
     wd = st->scratch;
+  }
+  if (linear_tc2_supported(dtype, M, K, N)) { // M > 128: SM-pair tiles (linear_tc2.cu)
+    return launch_linear_tc2(dtype, in, out, wd, bias, M, K, N, s);
   }
   constexpr int BN = 128, STAGES = 6;
   CUtensorMap tmA, tmB;

@@ -33,6 +33,29 @@ def test_linear_tc_fp(dtype, M, K, N, monkeypatch):
     assert np.abs(got - want).max() <= tol * max(1.0, np.abs(want).max())
 
 
+@pytest.mark.parametrize("bn", ["128", "256"])
+@pytest.mark.parametrize("M,K,N", [(129, 512, 256), (300, 1024, 1024), (512, 4096, 512), (1024, 1024, 768)])
+def test_linear_tc2_pair_tiles(M, K, N, bn, monkeypatch):
+    """The SM-pair (cta_group::2) kernel at both tile widths, ragged M (TMA zero-fill + row guard)."""
+    import torch
+    from flexflow_b200 import ops
+    monkeypatch.setenv("FFB_LINEAR", "tc")
+    monkeypatch.setenv("FFB_TC2_BN", bn)
+    rng = np.random.default_rng(33)
+    x = O.round_to_dt(rng.standard_normal((M, K)).astype(np.float32), "half")
+    w = O.round_to_dt((rng.standard_normal((N, K)) * 0.05).astype(np.float32), "half")
+    h = ops.FFHandler("cuda:0")
+    m = ops.LinearMeta(h, K, N, dtype=torch.float16, max_tokens_per_batch=1024)
+    out = torch.full((M, N), float("nan"), dtype=torch.float16, device="cuda")
+    ops.Linear.inference_kernel_wrapper(m, None, torch.from_numpy(x).cuda().half(), out, torch.from_numpy(w).cuda().half(),
+                                        None, K, N, M)
+    torch.cuda.synchronize()
+    want = O.linear(x, w, None, "half")
+    got = out.float().cpu().numpy()
+    assert np.isfinite(got).all()
+    assert np.abs(got - want).max() <= 2e-3 * max(1.0, np.abs(want).max())
+
+
 @pytest.mark.parametrize("quant", [8, 4])
 def test_linear_tc_quantised_matches_stream(quant, monkeypatch):
     """Large-M quantised path (dequant scratch + tcgen05 GEMM) against the oracle on the dequantised weights."""
