@@ -187,7 +187,7 @@ int linear_tc_supported(int dtype, int quant, int K, int N) {
   if (getenv("FFB_DISABLE_TC")) {
     return 0;
   }
-  return (dtype == FFB_DT_HALF || dtype == FFB_DT_BF16) && K % TC_BK == 0 && N % 128 == 0;
+  return (dtype == FFB_DT_HALF || dtype == FFB_DT_BF16) && K % TC_BK == 0 && N % 16 == 0;
 }
 
 LinearTcState *linear_tc_create(int dtype, int quant, int K, int N, int max_batch) {
@@ -228,7 +228,8 @@ int launch_linear_tc(LinearTcState *st, int dtype, int quant, void const *in, vo
     }
     wd = st->scratch;
   }
-  if (linear_tc2_supported(dtype, M, K, N)) { // M > 128: SM-pair tiles (linear_tc2.cu)
+  // M > 128 (or an N the 128-wide 1-SM tiles do not divide): SM-pair tiles (linear_tc2.cu)
+  if ((M > 128 || N % 128 != 0) && linear_tc2_supported(dtype, M, K, N)) {
     return launch_linear_tc2(dtype, in, out, wd, bias, M, K, N, s);
   }
   constexpr int BN = 128, STAGES = 6;

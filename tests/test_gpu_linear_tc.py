@@ -33,14 +33,15 @@ def test_linear_tc_fp(dtype, M, K, N, monkeypatch):
     assert np.abs(got - want).max() <= tol * max(1.0, np.abs(want).max())
 
 
-@pytest.mark.parametrize("bn", ["128", "256"])
-@pytest.mark.parametrize("M,K,N", [(129, 512, 256), (300, 1024, 1024), (512, 4096, 512), (1024, 1024, 768)])
+@pytest.mark.parametrize("bn", ["128", "256", "168", "80", "auto"])
+@pytest.mark.parametrize("M,K,N", [(129, 512, 256), (300, 1024, 1024), (512, 4096, 512), (1024, 1024, 768), (512, 512, 1248)])
 def test_linear_tc2_pair_tiles(M, K, N, bn, monkeypatch):
     """The SM-pair (cta_group::2) kernel at both tile widths, ragged M (TMA zero-fill + row guard)."""
     import torch
     from flexflow_b200 import ops
     monkeypatch.setenv("FFB_LINEAR", "tc")
-    monkeypatch.setenv("FFB_TC2_BN", bn)
+    if bn != "auto":
+        monkeypatch.setenv("FFB_TC2_BN", bn)  # widths that do not divide N exercise the partial last column tile
     rng = np.random.default_rng(33)
     x = O.round_to_dt(rng.standard_normal((M, K)).astype(np.float32), "half")
     w = O.round_to_dt((rng.standard_normal((N, K)) * 0.05).astype(np.float32), "half")

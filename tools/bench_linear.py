@@ -35,9 +35,13 @@ def main():
     h = ops.FFHandler("cuda:0")
     res = []
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    only_m = int(sys.argv[sys.argv.index("--m") + 1]) if "--m" in sys.argv else None
+    only_layer = sys.argv[sys.argv.index("--layer") + 1] if "--layer" in sys.argv else None
     for name, K, N in (("qkv_proj", 4096, 12288), ("o_proj", 4096, 4096)):
+        if only_layer and name != only_layer:
+            continue
         ws = [(torch.randn(N, K, device="cuda") * 0.02).half() for _ in range(4)]  # rotate weights: > L2
-        for M in ((16,) if "--decode-only" in sys.argv else (16, 64, 128, 256, 512, 1024)):
+        for M in ((only_m,) if only_m else (16,) if "--decode-only" in sys.argv else (16, 64, 128, 256, 512, 1024)):
             m = ops.LinearMeta(h, K, N, max_tokens_per_batch=1024)
             x = torch.randn(M, K, device="cuda").half()
             out = torch.empty(M, N, device="cuda", dtype=torch.float16)
@@ -47,7 +51,12 @@ def main():
                 i[0] += 1
                 ops.Linear.forward_kernel_wrapper(m, x, out, ws[i[0] % 4], None, K, N, M)
             ms = time_ms(fn)
-            ref = time_ms(lambda: torch.matmul(x, ws[0].t(), out=out))
+            j = [0]
+
+            def ref_fn():  # cuBLAS on the same rotating weights
+                j[0] += 1
+                torch.matmul(x, ws[j[0] % 4].t(), out=out)
+            ref = time_ms(ref_fn)
             flops = 2.0 * M * K * N
             res.append(dict(layer=name, M=M, K=K, N=N, ms=ms, tflops=flops / ms / 1e9, weight_gbs=K * N * 2 / ms / 1e6,
                             cublas_ms=ref, cublas_tflops=flops / ref / 1e9))
