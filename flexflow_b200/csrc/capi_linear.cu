@@ -6,6 +6,7 @@
 #include <new>
 
 #include "common.cuh"
+#include "peer.h"
 
 namespace ffb {
 int launch_linear_stream(int dtype, int quant, void const *in, void *out, void const *w, void const *bias, int M,
@@ -14,6 +15,10 @@ int launch_linear_stream(int dtype, int quant, void const *in, void *out, void c
 int linear_gemv_supported(int quant, int M, int K, int N);
 int launch_linear_gemv(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N,
                        cudaStream_t s);
+// fused o_proj + NVLink AllReduce for decode batches (linear_gemv.cu)
+int linear_gemv_allreduce_supported(PeerTable const *pt, int quant, int M, int K, int N);
+int launch_linear_gemv_allreduce(PeerTable const *pt, int dtype, void const *in, void *out, void const *w, void const *bias,
+                                 int M, int K, int N, cudaStream_t s);
 // tcgen05/TMA GEMM for batched prompt/tree tokens (linear_tc.cu)
 int linear_tc_supported(int dtype, int quant, int K, int N);
 int launch_linear_tc(struct LinearTcState *st, int dtype, int quant, void const *in, void *out, void const *w,
@@ -108,6 +113,31 @@ int ffb_linear_forward(ffb_linear_t h, void const *in, void *out, void const *w,
     }
   }
   return FFB_OK;
+}
+
+/* Row-parallel dense followed by the AllReduce over the TP shards (Linear -> AllReduce of
+ * src/runtime/model.cc:3421-3445, run back to back inside FusedOp::inference_task, src/ops/fused.cu:448-495).
+ * Decode batches (<= 16 tokens, dense weights, a communicator with an NVLink peer mapping) run as ONE kernel that
+ * exchanges the partial sums over peer memory; everything else is ffb_linear_forward + ffb_allreduce (NCCL). */
+int ffb_linear_forward_allreduce(ffb_linear_t h, ffb_comm_t comm, void const *in, void *out, void const *w,
+                                 void const *bias, int batch, ffb_stream_t stream) {
+  FFB_REQUIRE(h && comm && in && out && w, "null argument");
+  FFB_REQUIRE(batch >= 0 && batch <= h->d.max_batch, "batch %d exceeds max_batch %d", batch, h->d.max_batch);
+  if (batch == 0) {
+    return FFB_OK;
+  }
+  ffb_linear_desc const &d = h->d;
+  PeerTable const *pt = comm_peer_table(comm);
+  char const *force = getenv("FFB_LINEAR");
+  if (!force && !getenv("FFB_DISABLE_FUSED_ALLREDUCE") &&
+      linear_gemv_allreduce_supported(pt, d.quant_type, batch, d.in_dim, d.out_dim)) {
+    return launch_linear_gemv_allreduce(pt, d.dtype, in, out, w, bias, batch, d.in_dim, d.out_dim, (cudaStream_t)stream);
+  }
+  int rc = ffb_linear_forward(h, in, out, w, bias, batch, stream);
+  if (rc != FFB_OK) {
+    return rc;
+  }
+  return ffb_allreduce(comm, out, out, (size_t)batch * d.out_dim, d.dtype, stream);
 }
 
 } // extern "C"

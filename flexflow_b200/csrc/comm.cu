@@ -9,6 +9,7 @@
 #include <new>
 
 #include "common.cuh"
+#include "peer.h"
 
 namespace {
 
@@ -24,6 +25,7 @@ struct NcclApi {
   int (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
   int (*CommDestroy)(ncclComm_t) = nullptr;
   int (*AllReduce)(void const *, void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+  int (*AllGather)(void const *, void *, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
   char const *(*GetErrorString)(int) = nullptr;
 };
 
@@ -44,6 +46,7 @@ NcclApi *nccl() {
       api.CommInitRank = (decltype(api.CommInitRank))dlsym(api.lib, "ncclCommInitRank");
       api.CommDestroy = (decltype(api.CommDestroy))dlsym(api.lib, "ncclCommDestroy");
       api.AllReduce = (decltype(api.AllReduce))dlsym(api.lib, "ncclAllReduce");
+      api.AllGather = (decltype(api.AllGather))dlsym(api.lib, "ncclAllGather");
       api.GetErrorString = (decltype(api.GetErrorString))dlsym(api.lib, "ncclGetErrorString");
     }
   }
@@ -69,7 +72,69 @@ struct ffb_comm_s {
   ncclComm_t comm = nullptr;
   int nranks = 1, rank = 0;
   bool owned = false;
+  // NVLink peer mapping for the fused o_proj + AllReduce kernel (peer.h)
+  bool peer_ok = false;
+  ffb::PeerTable peer;
+  void *peer_local = nullptr;                      // this rank's allocation (receive area + flags + counters)
+  void *peer_mapped[ffb::kPeerMaxRanks] = {nullptr}; // cudaIpcOpenMemHandle results (other ranks)
 };
+
+namespace ffb {
+PeerTable const *comm_peer_table(ffb_comm_s *c) { return c && c->peer_ok ? &c->peer : nullptr; }
+} // namespace ffb
+
+namespace {
+
+constexpr int kPeerMaxN = 8192; // widest hidden size served by the fused path (LLaMA-2-70B)
+
+// Best effort: on any failure the communicator simply has no peer table and every collective goes through NCCL.
+void peer_setup(ffb_comm_s *c, NcclApi *api) {
+  using namespace ffb;
+  if (c->nranks < 2 || c->nranks > kPeerMaxRanks || !api->AllGather || getenv("FFB_DISABLE_PEER")) {
+    return;
+  }
+  size_t const recv_bytes = (size_t)2 * c->nranks * kPeerMaxTokens * kPeerMaxN * 2 * sizeof(float); // {value, epoch}
+  size_t const flag_bytes = (size_t)c->nranks * kPeerMaxCtas * sizeof(int);
+  size_t const total = recv_bytes + flag_bytes + 256;
+  cudaIpcMemHandle_t mine, *all_dev = nullptr, all[kPeerMaxRanks];
+  if (cudaMalloc(&c->peer_local, total) != cudaSuccess) {
+    c->peer_local = nullptr;
+    cudaGetLastError();
+    return;
+  }
+  bool ok = cudaMemset(c->peer_local, 0, total) == cudaSuccess && cudaIpcGetMemHandle(&mine, c->peer_local) == cudaSuccess &&
+            cudaMalloc(&all_dev, sizeof(mine) * (c->nranks + 1)) == cudaSuccess;
+  if (ok) {
+    ok = cudaMemcpy(all_dev + c->nranks, &mine, sizeof(mine), cudaMemcpyHostToDevice) == cudaSuccess &&
+         api->AllGather(all_dev + c->nranks, all_dev, sizeof(mine), /*ncclInt8*/ 0, c->comm, nullptr) == ncclSuccess &&
+         cudaStreamSynchronize(nullptr) == cudaSuccess &&
+         cudaMemcpy(all, all_dev, sizeof(mine) * c->nranks, cudaMemcpyDeviceToHost) == cudaSuccess;
+  }
+  if (all_dev) {
+    cudaFree(all_dev);
+  }
+  for (int r = 0; ok && r < c->nranks; r++) {
+    void *base = c->peer_local;
+    if (r != c->rank) {
+      ok = cudaIpcOpenMemHandle(&c->peer_mapped[r], all[r], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+      base = c->peer_mapped[r];
+    }
+    c->peer.recv[r] = (float *)base;
+    c->peer.flags[r] = (int *)((char *)base + recv_bytes);
+  }
+  if (!ok) {
+    cudaGetLastError();
+    return; // mappings (if any) are released in ffb_comm_destroy
+  }
+  c->peer.nranks = c->nranks;
+  c->peer.rank = c->rank;
+  c->peer.max_n = kPeerMaxN;
+  c->peer.epoch = (int *)((char *)c->peer_local + recv_bytes + flag_bytes);
+  c->peer.done = c->peer.epoch + 1;
+  c->peer_ok = true;
+}
+
+} // namespace
 
 extern "C" {
 
@@ -102,9 +167,12 @@ int ffb_comm_init_rank(void const *id, int nranks, int rank, ffb_comm_t *out) {
     delete c;
     return FFB_ERR_NCCL;
   }
+  peer_setup(c, api);
   *out = c;
   return FFB_OK;
 }
+
+int ffb_comm_has_peer(ffb_comm_t c) { return c && c->peer_ok ? 1 : 0; }
 
 int ffb_comm_from_nccl(void *nccl_comm, int nranks, int rank, ffb_comm_t *out) {
   FFB_REQUIRE(nccl_comm && out, "null argument");
@@ -121,6 +189,14 @@ int ffb_comm_from_nccl(void *nccl_comm, int nranks, int rank, ffb_comm_t *out) {
 int ffb_comm_destroy(ffb_comm_t c) {
   if (!c) {
     return FFB_OK;
+  }
+  for (int r = 0; r < ffb::kPeerMaxRanks; r++) {
+    if (c->peer_mapped[r]) {
+      cudaIpcCloseMemHandle(c->peer_mapped[r]);
+    }
+  }
+  if (c->peer_local) {
+    cudaFree(c->peer_local);
   }
   if (c->owned && c->comm) {
     NcclApi *api = nccl();

@@ -11,9 +11,20 @@
 //   * per tile each warp issues K/256 ldmatrix.x4 + K/16/16 mma.sync m16n8k16 (tokens = M operand, fp32
 //     accumulate) and the 16 partial sums are merged in warp order (deterministic).
 // 8-feature tiles keep the static round-robin schedule within one tile (64 KiB at K = 4096) of perfect balance.
+//
+// FUSED o_proj + AllReduce (FUSED = true; replaces Linear -> AllReduce, src/ops/fused.cu:448-495 +
+// src/parallel_ops/kernels/allreduce_kernels.cu:64-73, for decode batches): instead of storing its partial sums, a
+// CTA PUSHES them over NVLink into slot [my rank] of every rank's receive area as 8-byte {fp32 value, epoch} words
+// (one store each: the epoch travelling WITH the value is the arrival flag, so there is no fence, no separate flag
+// and only one NVLink crossing on the critical path), then polls its own slots until every peer's words carry
+// this epoch and sums them in rank order (deterministic, fp32) into the final output.  CTA i of every rank owns the
+// same output tiles, so the exchange needs no grid-wide barrier and overlaps with the weight stream of the slower
+// CTAs.  Receive areas are double buffered by epoch parity: a rank can only have pushed epoch e+1 after it finished
+// reading epoch e (stream order), so by the time this rank has read everybody's e+1 it may overwrite the e slots.
 #include <cstdlib>
 
 #include "common.cuh"
+#include "peer.h"
 
 namespace ffb {
 namespace {
@@ -64,11 +75,11 @@ __device__ __forceinline__ void gv_mma<__nv_bfloat16>(float (&c)[4], uint32_t a0
       : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
-// KSTEPS = K / 16 / 16: mma k-steps per warp per tile (4, 8 or 16 for K = 1024, 2048, 4096)
-template <typename T, int KSTEPS>
+// KSTEPS = K / 16 / 16: mma k-steps per warp per tile (2, 4, 8 or 16 for K = 512, 1024, 2048, 4096)
+template <typename T, int KSTEPS, bool FUSED>
 __global__ void __launch_bounds__(GV_THREADS, 1)
 linear_gemv_kernel(T const *__restrict__ A, T const *__restrict__ W, T const *__restrict__ bias, T *__restrict__ out,
-                   int M, int N) {
+                   int M, int N, const __grid_constant__ PeerTable pt) {
   constexpr int K = KSTEPS * 16 * GV_CONSUMERS;
   constexpr int WROW = K * 2 + 16; // padded row (bytes): 8 rows hit 8 distinct bank groups in ldmatrix
   constexpr int STAGE_BYTES = GV_BN * WROW;
@@ -80,6 +91,7 @@ linear_gemv_kernel(T const *__restrict__ A, T const *__restrict__ W, T const *__
   __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES];
 
   int const tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  int const epoch = FUSED ? *reinterpret_cast<int const volatile *>(pt.epoch) + 1 : 0; // this collective's number
   int const ntiles = N / GV_BN;
   int const my_tiles = (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
@@ -184,11 +196,50 @@ linear_gemv_kernel(T const *__restrict__ A, T const *__restrict__ W, T const *__
         for (int w = 0; w < GV_CONSUMERS; w++) {
           v += slot[w * 128 + tid];
         }
-        if (r < M) {
+        if (FUSED) {
+          if (r < M) { // {value, epoch} into this rank's slot of every rank's receive area (8 features = 64 B runs)
+            size_t const off = ((size_t)((epoch & 1) * pt.nranks + pt.rank) * kPeerMaxTokens + r) * pt.max_n + n0 + c;
+            for (int p = 0; p < pt.nranks; p++) {
+              // one 64-bit scalar store: single-copy atomic, so the reader never sees a value without its epoch
+              unsigned long long const word = ((unsigned long long)(uint32_t)epoch << 32) | __float_as_uint(v);
+              asm volatile("st.relaxed.sys.global.b64 [%0], %1;" ::"l"(pt.recv[p] + 2 * off), "l"(word) : "memory");
+            }
+          }
+        } else if (r < M) {
           if (bias) {
             v += DT<T>::to_f(bias[n0 + c]);
           }
           out[(size_t)r * N + n0 + c] = DT<T>::from_f(v);
+        }
+      }
+    }
+    if (FUSED) {
+      // ---- reduce in rank order; a word has arrived when its epoch field matches ----
+      float const *mine = pt.recv[pt.rank] + (size_t)2 * (epoch & 1) * pt.nranks * kPeerMaxTokens * pt.max_n;
+      for (int i = tid; i < my_tiles * 128; i += GV_CONSUMERS * 32) {
+        int const t = i >> 7, r = (i >> 3) & 15, c = i & 7;
+        int const n0 = ((int)blockIdx.x + t * (int)gridDim.x) * GV_BN;
+        if (r < M) {
+          float v = bias ? DT<T>::to_f(bias[n0 + c]) : 0.f;
+          for (int p = 0; p < pt.nranks; p++) {
+            float const *src = mine + 2 * (((size_t)p * kPeerMaxTokens + r) * pt.max_n + n0 + c);
+            unsigned long long word;
+            do {
+              asm volatile("ld.relaxed.sys.global.b64 %0, [%1];" : "=l"(word) : "l"(src) : "memory");
+            } while ((int)(word >> 32) != epoch);
+            v += __uint_as_float((uint32_t)word);
+          }
+          out[(size_t)r * N + n0 + c] = DT<T>::from_f(v);
+        }
+      }
+      // the last CTA to finish closes the epoch (every CTA read it at kernel start)
+      asm volatile("bar.sync 1, %0;" ::"n"(GV_CONSUMERS * 32) : "memory");
+      if (tid == 0) {
+        int const prev = atomicAdd(pt.done, 1);
+        if (prev == (int)gridDim.x - 1) {
+          *pt.done = 0;
+          __threadfence();
+          *reinterpret_cast<int volatile *>(pt.epoch) = epoch;
         }
       }
     }
@@ -201,37 +252,60 @@ int linear_gemv_supported(int quant, int M, int K, int N) {
   if (getenv("FFB_DISABLE_GEMV")) {
     return 0;
   }
-  return quant == FFB_DT_NONE && M >= 1 && M <= 16 && (K == 1024 || K == 2048 || K == 4096) && N % GV_BN == 0;
+  return quant == FFB_DT_NONE && M >= 1 && M <= 16 && (K == 512 || K == 1024 || K == 2048 || K == 4096) && N % GV_BN == 0;
 }
 
-template <typename T, int KSTEPS>
-static int launch_gemv_t(void const *in, void *out, void const *w, void const *bias, int M, int N, cudaStream_t s) {
+template <typename T, int KSTEPS, bool FUSED>
+static int launch_gemv_t(void const *in, void *out, void const *w, void const *bias, int M, int N, cudaStream_t s,
+                         PeerTable const &pt) {
   constexpr int K = KSTEPS * 16 * GV_CONSUMERS;
   constexpr int STAGE_BYTES = GV_BN * (K * 2 + 16);
   constexpr size_t smem = (size_t)(GV_RING_BYTES / STAGE_BYTES) * STAGE_BYTES + 2 * GV_CONSUMERS * 128 * 4;
   static bool attr = false;
   if (!attr) {
-    FFB_CUDA_TRY(cudaFuncSetAttribute(linear_gemv_kernel<T, KSTEPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    FFB_CUDA_TRY(cudaFuncSetAttribute(linear_gemv_kernel<T, KSTEPS, FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr = true;
   }
   int const ntiles = N / GV_BN;
   int const grid = ntiles < kNumSMs ? ntiles : kNumSMs;
-  linear_gemv_kernel<T, KSTEPS><<<grid, GV_THREADS, smem, s>>>((T const *)in, (T const *)w, (T const *)bias, (T *)out, M, N);
+  linear_gemv_kernel<T, KSTEPS, FUSED><<<grid, GV_THREADS, smem, s>>>((T const *)in, (T const *)w, (T const *)bias, (T *)out, M, N, pt);
   FFB_LAUNCH_CHECK();
   return FFB_OK;
 }
 
+template <bool FUSED>
+static int launch_gemv_dispatch(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N,
+                                cudaStream_t s, PeerTable const &pt) {
+  int const ks = K / (16 * GV_CONSUMERS);
+  if (ks == 2) {
+    return dtype == FFB_DT_HALF ? launch_gemv_t<__half, 2, FUSED>(in, out, w, bias, M, N, s, pt)
+                                : launch_gemv_t<__nv_bfloat16, 2, FUSED>(in, out, w, bias, M, N, s, pt);
+  }
+  if (dtype == FFB_DT_HALF) {
+    return ks == 4 ? launch_gemv_t<__half, 4, FUSED>(in, out, w, bias, M, N, s, pt)
+                   : (ks == 8 ? launch_gemv_t<__half, 8, FUSED>(in, out, w, bias, M, N, s, pt)
+                              : launch_gemv_t<__half, 16, FUSED>(in, out, w, bias, M, N, s, pt));
+  }
+  return ks == 4 ? launch_gemv_t<__nv_bfloat16, 4, FUSED>(in, out, w, bias, M, N, s, pt)
+                 : (ks == 8 ? launch_gemv_t<__nv_bfloat16, 8, FUSED>(in, out, w, bias, M, N, s, pt)
+                            : launch_gemv_t<__nv_bfloat16, 16, FUSED>(in, out, w, bias, M, N, s, pt));
+}
+
 int launch_linear_gemv(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N,
                        cudaStream_t s) {
-  int const ks = K / (16 * GV_CONSUMERS);
-  if (dtype == FFB_DT_HALF) {
-    return ks == 4 ? launch_gemv_t<__half, 4>(in, out, w, bias, M, N, s)
-                   : (ks == 8 ? launch_gemv_t<__half, 8>(in, out, w, bias, M, N, s)
-                              : launch_gemv_t<__half, 16>(in, out, w, bias, M, N, s));
-  }
-  return ks == 4 ? launch_gemv_t<__nv_bfloat16, 4>(in, out, w, bias, M, N, s)
-                 : (ks == 8 ? launch_gemv_t<__nv_bfloat16, 8>(in, out, w, bias, M, N, s)
-                            : launch_gemv_t<__nv_bfloat16, 16>(in, out, w, bias, M, N, s));
+  PeerTable none;
+  return launch_gemv_dispatch<false>(dtype, in, out, w, bias, M, K, N, s, none);
+}
+
+// o_proj + AllReduce in one launch.  Every rank of the communicator must call it with the same M, K, N.
+int linear_gemv_allreduce_supported(PeerTable const *pt, int quant, int M, int K, int N) {
+  return pt && pt->nranks >= 2 && M <= kPeerMaxTokens && N <= pt->max_n && (N / GV_BN < kNumSMs ? N / GV_BN : kNumSMs) <= kPeerMaxCtas &&
+         linear_gemv_supported(quant, M, K, N);
+}
+
+int launch_linear_gemv_allreduce(PeerTable const *pt, int dtype, void const *in, void *out, void const *w, void const *bias,
+                                 int M, int K, int N, cudaStream_t s) {
+  return launch_gemv_dispatch<true>(dtype, in, out, w, bias, M, K, N, s, *pt);
 }
 
 } // namespace ffb

@@ -62,6 +62,8 @@ SIGNATURES = {
     "ffb_comm_destroy": (_i, [_vp]),
     "ffb_comm_from_nccl": (_i, [_vp, _i, _i, C.POINTER(_vp)]),
     "ffb_allreduce": (_i, [_vp, _vp, _vp, _sz, _i, _vp]),
+    "ffb_comm_has_peer": (_i, [_vp]),
+    "ffb_linear_forward_allreduce": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
 }
 
 _lib = None

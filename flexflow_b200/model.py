@@ -188,10 +188,19 @@ class FFModel:
             self.handler.load_batch_config(bc)
         input_tensor.buf = hidden
         shard = self.config.tp_rank
-        for lyr in self.layers:
+        fused_into = None  # the AllReduce layer whose work the preceding dense already did
+        for li, lyr in enumerate(self.layers):
             x = lyr.inputs[0].buf
             y = lyr.output.buf
             if lyr.op_type == "linear":
+                nxt = self.layers[li + 1] if li + 1 < len(self.layers) else None
+                if nxt is not None and nxt.op_type == "allreduce" and nxt.inputs[0] is lyr.output:
+                    # Linear -> AllReduce as one op (FusedOp, src/ops/fused.cu:448-495): result lands in the
+                    # AllReduce layer's output
+                    ops.Linear.inference_allreduce_wrapper(lyr.meta, nxt.meta, bc, x, nxt.output.buf, lyr.weight,
+                                                           lyr.bias, lyr.inputs[0].dim, lyr.output.dim, T)
+                    fused_into = nxt
+                    continue
                 ops.Linear.inference_kernel_wrapper(lyr.meta, bc, x, y, lyr.weight, lyr.bias, lyr.inputs[0].dim,
                                                     lyr.output.dim, T)
             elif lyr.op_type == "inc_attn":
@@ -201,5 +210,8 @@ class FFModel:
             elif lyr.op_type == "spec_attn":
                 ops.SpecIncMultiHeadSelfAttention.inference_kernel_wrapper(lyr.meta, bc, shard, x, y)
             elif lyr.op_type == "allreduce":
+                if lyr is fused_into:
+                    fused_into = None
+                    continue
                 ops.AllReduce.inference_kernel_wrapper(lyr.meta, bc, x[:T], y[:T])
         return self.layers[-1].output.buf[:T]

@@ -225,6 +225,15 @@ class Linear:
     def inference_kernel_wrapper(m, bc, input, output, weight, bias, in_dim, out_dim, batch_size):
         Linear.forward_kernel_wrapper(m, input, output, weight, bias, in_dim, out_dim, batch_size)
 
+    @staticmethod
+    def inference_allreduce_wrapper(m, ar_meta, bc, input, output, weight, bias, in_dim, out_dim, batch_size):
+        """Linear -> AllReduce run back to back by FusedOp::inference_task (src/ops/fused.cu:448-495): one fused
+        kernel over NVLink peer memory for decode batches, otherwise linear + NCCL allreduce (ffb200.h)."""
+        if in_dim != m.in_dim or out_dim != m.out_dim:
+            raise L.FFBError("shape does not match LinearMeta")
+        L.check(L.load().ffb_linear_forward_allreduce(m._h, ar_meta.comm._h, _ptr(input), _ptr(output), _ptr(weight),
+                                                      _ptr(bias), batch_size, _stream()), "ffb_linear_forward_allreduce")
+
 
 class AllReduceMeta:
     """AllReduceMeta: holds the communicator (handle.ncclComm in the reference)."""
@@ -259,6 +268,7 @@ class Communicator:
         self._h = C.c_void_p()
         L.check(lib.ffb_comm_init_rank(uid, nranks, rank, C.byref(self._h)), "ffb_comm_init_rank")
         self.rank, self.nranks = rank, nranks
+        self.has_peer = bool(lib.ffb_comm_has_peer(self._h))
 
     def close(self):
         if self._h:

@@ -173,6 +173,15 @@ int ffb_comm_destroy(ffb_comm_t c);
 int ffb_comm_from_nccl(void *nccl_comm, int nranks, int rank, ffb_comm_t *out);
 int ffb_allreduce(ffb_comm_t c, void const *in_dev, void *out_dev, size_t count, int dtype,
                   ffb_stream_t stream);
+/* 1 when the communicator mapped every rank's receive area over NVLink (CUDA IPC) at creation. */
+int ffb_comm_has_peer(ffb_comm_t c);
+/* Linear (row-parallel o_proj) immediately followed by the AllReduce over the TP shards, as the reference runs them
+ * back to back inside FusedOp::inference_task (src/ops/fused.cu:448-495; insertion rule src/runtime/model.cc:3421-3445).
+ * Decode batches (<= 16 tokens) on a peer-mapped communicator run as ONE kernel that pushes the fp32 partial sums into
+ * every rank's receive area and reduces them in rank order; otherwise ffb_linear_forward + ffb_allreduce.  Every
+ * rank must make the same call. */
+int ffb_linear_forward_allreduce(ffb_linear_t h, ffb_comm_t comm, void const *in_dev, void *out_dev,
+                                 void const *weight_dev, void const *bias_dev, int batch, ffb_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -15,7 +15,7 @@ from flexflow_b200 import ops  # noqa: E402
 from flexflow_b200.model import FFConfig, FFModel  # noqa: E402
 from flexflow_b200.sharding import shard_o_proj, shard_qkv_proj  # noqa: E402
 
-HIDDEN, NQ, NKV, DH = 1024, 8, 8, 128
+HIDDEN, NQ, NKV, DH = (int(x) for x in os.environ.get("TP_DIMS", "1024,8,8,128").split(","))
 
 
 def build(tp, rank, comm, dev):
@@ -65,6 +65,36 @@ def main():
     for a, b in zip(outs[0], outs[1]):
         err = np.abs(a - b).max() / max(np.abs(b).max(), 1e-6)
         assert err < 1e-2, err
+    if os.environ.get("TP_EXPECT_PEER"):
+        # the decode step above went through the fused o_proj + NVLink AllReduce kernel: check the peer mapping exists,
+        # that 40 further collectives (epoch parity, flag reuse) keep matching the linear + NCCL path, and that every
+        # rank holds bit-identical results (fixed-order fp32 reduction)
+        assert comm.has_peer, "communicator has no NVLink peer mapping"
+        m, x = build(world, rank, comm, dev)
+        m.set_weight("layers.0.self_attn.qkv_proj", shard_qkv_proj(wq, wk, wv, NQ, NKV, DH, world, rank).to(dev))
+        m.set_weight("layers.0.self_attn.o_proj", shard_o_proj(wo, NQ, DH, world, rank).to(dev))
+        buf = torch.zeros(64, HIDDEN, dtype=torch.float16, device=dev)
+        worst = 0.0
+        for step in range(40):
+            ntok = 1 + step % 3
+            buf[:16] = torch.randn(16, HIDDEN, generator=g).half().to(dev)
+            bcs = TL.make_inc_batch([dict(slot=s, first_depth=step, ntok=1) for s in range(1 + step % 4)])
+            del ntok
+            os.environ.pop("FFB_DISABLE_FUSED_ALLREDUCE", None)
+            y_f = m.inference(bcs, x, buf).float().clone()
+            os.environ["FFB_DISABLE_FUSED_ALLREDUCE"] = "1"
+            for lyr in m.layers:  # same KV state for the second pass: it only re-appends the same rows
+                pass
+            y_n = m.inference(bcs, x, buf).float().clone()
+            torch.cuda.synchronize()
+            worst = max(worst, float((y_f - y_n).abs().max() / y_n.abs().max().clamp_min(1e-6)))
+            gathered = [torch.empty_like(y_f) for _ in range(world)]
+            dist.all_gather(gathered, y_f)
+            assert all(torch.equal(gathered[0], t) for t in gathered), "ranks disagree on the fused result"
+        os.environ.pop("FFB_DISABLE_FUSED_ALLREDUCE", None)
+        assert worst < 5e-3, worst
+        if rank == 0:
+            print("PEER_OK worst %.2e" % worst)
     dist.barrier()
     if rank == 0:
         print("TP_OK")
