@@ -174,11 +174,15 @@ int make_tensor_map_2d(CUtensorMap *tm, int dtype, void const *ptr, long rows, i
 
 int linear_tc2_supported(int dtype, int M, int K, int N);
 int launch_linear_tc2(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N,
-                      cudaStream_t s);
+                      void *ws, int *cnt, cudaStream_t s);
+size_t linear_tc2_ws_bytes();
+size_t linear_tc2_cnt_bytes();
 
 struct LinearTcState {
   int dtype, quant, K, N, max_batch;
   void *scratch = nullptr; // dequantised weights [N][K] DT (quantised layers only)
+  void *splitk_ws = nullptr; // fp32 partial tiles of the split-K SM-pair GEMM (linear_tc2.cu)
+  int *splitk_cnt = nullptr; // its arrival counters (zero between launches)
   bool attr_set[2] = {false, false};
 };
 
@@ -189,6 +193,8 @@ int linear_tc_supported(int dtype, int quant, int K, int N) {
   }
   return (dtype == FFB_DT_HALF || dtype == FFB_DT_BF16) && K % TC_BK == 0 && N % 16 == 0;
 }
+
+void linear_tc_destroy(LinearTcState *st);
 
 LinearTcState *linear_tc_create(int dtype, int quant, int K, int N, int max_batch) {
   LinearTcState *st = new (std::nothrow) LinearTcState();
@@ -205,6 +211,16 @@ LinearTcState *linear_tc_create(int dtype, int quant, int K, int N, int max_batc
       return nullptr;
     }
   }
+  // split-K only pays when the output has fewer 256 x 256 tiles than SM pairs at some batch size <= max_batch
+  if (max_batch > 128 && (N + 255) / 256 < kNumSMs / 2 && !getenv("FFB_DISABLE_TC2_SPLITK")) {
+    if (cudaMalloc(&st->splitk_ws, linear_tc2_ws_bytes()) != cudaSuccess ||
+        cudaMalloc((void **)&st->splitk_cnt, linear_tc2_cnt_bytes()) != cudaSuccess ||
+        cudaMemset(st->splitk_cnt, 0, linear_tc2_cnt_bytes()) != cudaSuccess) {
+      set_error("cudaMalloc of the split-K workspace failed: %s", cudaGetErrorString(cudaGetLastError()));
+      linear_tc_destroy(st);
+      return nullptr;
+    }
+  }
   return st;
 }
 
@@ -212,6 +228,12 @@ void linear_tc_destroy(LinearTcState *st) {
   if (st) {
     if (st->scratch) {
       cudaFree(st->scratch);
+    }
+    if (st->splitk_ws) {
+      cudaFree(st->splitk_ws);
+    }
+    if (st->splitk_cnt) {
+      cudaFree(st->splitk_cnt);
     }
     delete st;
   }
@@ -230,7 +252,7 @@ int launch_linear_tc(LinearTcState *st, int dtype, int quant, void const *in, vo
   }
   // M > 128 (or an N the 128-wide 1-SM tiles do not divide): SM-pair tiles (linear_tc2.cu)
   if ((M > 128 || N % 128 != 0) && linear_tc2_supported(dtype, M, K, N)) {
-    return launch_linear_tc2(dtype, in, out, wd, bias, M, K, N, s);
+    return launch_linear_tc2(dtype, in, out, wd, bias, M, K, N, st->splitk_ws, st->splitk_cnt, s);
   }
   constexpr int BN = 128, STAGES = 6;
   CUtensorMap tmA, tmB;

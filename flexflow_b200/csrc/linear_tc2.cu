@@ -13,6 +13,7 @@
 // epilogue warps of each CTA read it with tcgen05.ld, add the bias, convert and store.
 // The reference accumulates in DT (cuBLAS compute type = output type); fp32 here.
 #include <algorithm>
+#include <cstdio>
 #include <type_traits>
 
 #include "tc_common.cuh"
@@ -58,6 +59,33 @@ __device__ __forceinline__ void tc_commit_2sm(uint64_t *bar) {
                ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
 }
 
+// 16 fp32 accumulator columns (+ bias) -> 16 DT values, two 16-byte stores
+template <typename T, int OFF = 0, int NR>
+__device__ __forceinline__ void emit16(uint32_t const (&r)[NR], T *dst, T const *bias) {
+#pragma unroll
+  for (int v = 0; v < 2; v++) {
+    float f[8];
+#pragma unroll
+    for (int e = 0; e < 8; e++) {
+      f[e] = __uint_as_float(r[OFF + v * 8 + e]);
+      if (bias) {
+        f[e] += DT<T>::to_f(bias[v * 8 + e]);
+      }
+    }
+    *reinterpret_cast<uint4 *>(dst + v * 8) = pack8<T>(f);
+  }
+}
+// N % 16 == 0: each 16-column half of a 32-column group is entirely inside or outside the matrix
+template <typename T>
+__device__ __forceinline__ void emit32(uint32_t const (&r)[32], T *orow, T const *bias, int col, bool row_ok, int N) {
+  if (row_ok && col < N) {
+    emit16<T, 0>(r, orow + col, bias ? bias + col : nullptr);
+    if (col + 16 < N) {
+      emit16<T, 16>(r, orow + col + 16, bias ? bias + col + 16 : nullptr);
+    }
+  }
+}
+
 // BN (tile width, a multiple of 16 up to 256) and the ring depth are run-time values: the host picks the width that
 // fills the 74 SM pairs in whole waves (e.g. 168 for M = 512, N = 12288: 2 x 74 tiles).
 // PERSISTENT: cluster c works on tiles c, c + #clusters, ...; the accumulator is double-buffered in tensor memory
@@ -65,28 +93,55 @@ __device__ __forceinline__ void tc_commit_2sm(uint64_t *bar) {
 // and the launch / barrier / TMEM set-up cost is paid once per SM pair, not once per tile.
 constexpr int T2_MAX_STAGES = 10;
 
+// split-K work unit u = (tile u / S, k-slice u % S): the slices of a tile, which wait for each other in the epilogue,
+// run on neighbouring clusters (scheduled together)
+__device__ __forceinline__ int unit_slice(int u, int S) { return S == 1 ? 0 : u % S; }
+
+#ifdef FFB_TC2_TRACE_BUILD
+// nvcc -DFFB_TC2_TRACE_BUILD + env FFB_TC2_TRACE=1: the leader CTA of cluster 0 stamps %globaltimer at its phase
+// boundaries for 8 consecutive launches (row = launch % 8); dumped by the host after every 8th launch
+__device__ long long g_tc2_trace[8][16];
+__device__ int g_tc2_launch;
+#define T2_TR(ev)                                                                  \
+  do {                                                                             \
+    if (blockIdx.x == 0) {                                                         \
+      long long t_;                                                                \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                       \
+      g_tc2_trace[*(volatile int *)&g_tc2_launch & 7][ev] = t_;                    \
+    }                                                                              \
+  } while (0)
+#else
+#define T2_TR(ev) ((void)0)
+#endif
+
 template <typename T>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T2_THREADS, 1)
 linear_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  T *__restrict__ out, T const *__restrict__ bias, int M, int N, int K, int BN, int STAGES) {
+                  T *__restrict__ out, T const *__restrict__ bias, int M, int N, int K, int BN, int STAGES,
+                  int S, float4 *__restrict__ ws, int *__restrict__ cnt) {
   constexpr uint32_t A_BYTES = T2_BM * T2_BK * 2;
   uint32_t const B_BYTES = (uint32_t)(BN / 2) * T2_BK * 2; // a multiple of 1024 (BN % 16 == 0)
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[T2_MAX_STAGES], empty_bar[T2_MAX_STAGES];
   __shared__ __align__(8) uint64_t tmem_full_bar[2], tmem_empty_bar[2];
+  __shared__ __align__(8) uint64_t part_bar[4][4]; // split-K: partial of epilogue warp q, 64-column chunk c has landed
   __shared__ uint32_t tmem_base_smem;
   // 128B-swizzled tiles need 1024-byte alignment; both CTAs compute the same offsets (the MMA addresses the peer's
   // shared memory with the leader's descriptors)
   uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t *sA = smem, *sB = smem + STAGES * A_BYTES;
+  uint8_t *stage_out = sB + STAGES * B_BYTES; // 4 epilogue warps x 4 KB (a multiple of 1024 from smem)
 
   int const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint32_t const rank = cluster_ctarank(); // 0 = leader
   int const num_k = K / T2_BK;
   int const m_tiles = (M + 255) / 256, n_tiles = (N + BN - 1) / BN, tiles = m_tiles * n_tiles;
   int const cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+  // split-K: work unit u = (tile u / S, k-slice u % S); slice ks covers k-blocks [ks*num_k/S, (ks+1)*num_k/S)
+  int const units = tiles * S;
 
   if (warp == 0 && lane == 0) {
+    T2_TR(0);
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
   }
@@ -98,6 +153,9 @@ linear_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     for (int b = 0; b < 2; b++) {
       mbar_init(&tmem_full_bar[b], 1);  // multicast tcgen05.commit
       mbar_init(&tmem_empty_bar[b], 8); // (leader's copy is used) one arrive per epilogue warp of both CTAs
+    }
+    for (int i = 0; i < 16; i++) {
+      mbar_init(&part_bar[i >> 2][i & 3], 1);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -113,9 +171,12 @@ linear_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 0 && lane == 0) {
     // ===== TMA producer (both CTAs): this CTA's half of A and of W =====
     int it = 0; // ring item counter, runs across tiles
-    for (int t = cluster_id; t < tiles; t += num_clusters) {
+    T2_TR(1);
+    for (int u = cluster_id; u < units; u += num_clusters) {
+      int const t = u / S, ks = unit_slice(u, S);
       int const m_blk = t % m_tiles, n_blk = t / m_tiles;
-      for (int kb = 0; kb < num_k; kb++, it++) {
+      int const kb1 = (ks + 1) * num_k / S;
+      for (int kb = ks * num_k / S; kb < kb1; kb++, it++) {
         int const s = it % STAGES;
         uint32_t const ph = (it / STAGES) & 1;
         mbar_wait(&empty_bar[s], ph ^ 1);
@@ -127,6 +188,7 @@ linear_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         tma_load_2d_2sm(smem_u32(sB + s * B_BYTES), &tmB, kb * T2_BK, n_blk * BN + (int)rank * (BN / 2), leader_full);
       }
     }
+    T2_TR(2);
   } else if (warp == 1 && lane == 0) {
     if (rank == 0) {
       // ===== MMA issuer (leader CTA only) =====
@@ -134,59 +196,175 @@ linear_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       constexpr uint32_t fmt = std::is_same<T, __nv_bfloat16>::value ? 1u : 0u;
       uint32_t const idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
       int it = 0, i = 0;
-      for (int t = cluster_id; t < tiles; t += num_clusters, i++) {
+      for (int u = cluster_id; u < units; u += num_clusters, i++) {
         int const b = i & 1;
         mbar_wait(&tmem_empty_bar[b], ((i >> 1) & 1) ^ 1); // both CTAs' epilogues have drained this buffer
         tc_fence_after();
         uint32_t const tmem_d = tmem_base + (uint32_t)b * 256u;
-        for (int kb = 0; kb < num_k; kb++, it++) {
+        int const ks = unit_slice(u, S), kb0 = ks * num_k / S, kb1 = (ks + 1) * num_k / S;
+        for (int kb = kb0; kb < kb1; kb++, it++) {
           int const s = it % STAGES;
           uint32_t const ph = (it / STAGES) & 1;
           mbar_wait(&full_bar[s], ph);
+          if (it == 0) {
+            T2_TR(3);
+          }
           tc_fence_after();
           uint64_t const da = umma_desc_sw128(smem_u32(sA + s * A_BYTES));
           uint64_t const db = umma_desc_sw128(smem_u32(sB + s * B_BYTES));
 #pragma unroll
           for (int k = 0; k < T2_BK / 16; k++) {
             // advance 16 elements (32 B) along K inside the swizzle atom: start-address field += 2
-            tc_mma_f16_2sm(tmem_d, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+            tc_mma_f16_2sm(tmem_d, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, ((kb - kb0) | k) != 0);
           }
           tc_commit_2sm(&empty_bar[s]); // slot reusable in BOTH CTAs once these MMAs have read it
         }
         tc_commit_2sm(&tmem_full_bar[b]);
       }
+      T2_TR(4);
     }
   } else if (warp >= 4) {
     // ===== epilogue (both CTAs): this CTA's 128 x BN half of the accumulator, TMEM -> registers -> global =====
     int const q = warp & 3; // this warp may touch TMEM lanes [32q, 32q+32)
     int i = 0;
-    for (int t = cluster_id; t < tiles; t += num_clusters, i++) {
+    for (int u = cluster_id; u < units; u += num_clusters, i++) {
+      int const t = u / S;
       int const m_blk = t % m_tiles, n_blk = t / m_tiles;
       int const b = i & 1;
       mbar_wait(&tmem_full_bar[b], (i >> 1) & 1);
+      if (warp == 4 && lane == 0) {
+        T2_TR(5);
+      }
       tc_fence_after();
       int const row = m_blk * 256 + (int)rank * T2_BM + q * 32 + lane;
       uint32_t const tsrc = tmem_base + (uint32_t)b * 256u + ((uint32_t)(q * 32) << 16);
+      // ----- split-K (S == 2): the two k-slices of a tile run on neighbouring SM pairs and EXCHANGE halves: slice 0
+      // finishes the low 64-column chunks of the tile, slice 1 the high ones.  Each warp first parks the chunks it
+      // does not finish as fp32 in the L2 workspace (per 16 columns: 4 x 32 lanes x float4, so that its stores and
+      // the partner's bulk copies are contiguous) and raises a flag; then it waits for the partner warp (same rows),
+      // bulk-copies the partner's partial of ITS chunks into the operand ring - idle by now: every MMA of this
+      // CTA's only unit has completed - one mbarrier per chunk, and adds it to the accumulator below.  A two-term
+      // fp32 sum does not depend on which side adds, so the result is deterministic. -----
+      int const nchunk = (BN + 63) >> 6;
+      int c_begin = 0, c_end = nchunk;
+      uint8_t *const part = smem + (size_t)q * (BN >> 4) * 2048;
+      if (S == 2) {
+        int const ks = unit_slice(u, S), wid = (int)rank * 4 + q, half = nchunk >> 1;
+        c_begin = ks ? half : 0;
+        c_end = ks ? nchunk : half;
+        int const o_begin = ks ? 0 : half, o_end = ks ? half : nchunk;
+        float4 *const my = ws + ((size_t)((t * 2 + ks) * 8 + wid) * (BN >> 4)) * 128 + lane;
+        uint32_t ra[32], rb[32];
+        if (o_begin < o_end) {
+          tmem_ld32_nowait(tsrc + (uint32_t)(o_begin * 64), ra);
+          tmem_ld32_nowait(tsrc + (uint32_t)(o_begin * 64 + 32), rb);
+        }
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 16) {
-        uint32_t r[16];
-        tmem_ld16(tsrc + (uint32_t)c0, r);
-        int const col = n_blk * BN + c0;
-        if (row < M && col < N) { // N % 16 == 0: a 16-column chunk is entirely inside or outside the matrix
-          T *dst = out + (size_t)row * N + col;
+        for (int c = o_begin; c < o_end; c++) {
+          int const c0 = c * 64;
+          tmem_ld_wait32(ra);
+          reg_tie32(rb);
 #pragma unroll
-          for (int v = 0; v < 2; v++) {
-            float f[8];
-#pragma unroll
-            for (int e = 0; e < 8; e++) {
-              f[e] = __uint_as_float(r[v * 8 + e]);
-              if (bias) {
-                f[e] += DT<T>::to_f(bias[col + v * 8 + e]);
-              }
+          for (int j = 0; j < 16; j++) {
+            if (c0 + j * 4 < BN) {
+              uint32_t const *r = j < 8 ? &ra[j * 4] : &rb[(j - 8) * 4];
+              __stcg(my + ((c0 >> 2) + j) * 32, make_float4(__uint_as_float(r[0]), __uint_as_float(r[1]),
+                                                            __uint_as_float(r[2]), __uint_as_float(r[3])));
             }
-            *reinterpret_cast<uint4 *>(dst + v * 8) = pack8<T>(f);
+          }
+          if (c + 1 < o_end) {
+            tmem_ld32_nowait(tsrc + (uint32_t)(c0 + 64), ra);
+            tmem_ld32_nowait(tsrc + (uint32_t)(c0 + 96), rb);
           }
         }
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) {
+          atomicExch(&cnt[(t * 2 + ks) * 8 + wid], 1);
+          int *const theirs = cnt + (t * 2 + (ks ^ 1)) * 8 + wid;
+          int seen;
+          do {
+            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(theirs) : "memory");
+          } while (seen == 0);
+          *theirs = 0; // ready for the next launch on this stream (the partner only writes its flag once)
+          asm volatile("fence.proxy.async;" ::: "memory"); // the partials were written through the generic proxy
+          float4 const *const src = ws + ((size_t)((t * 2 + (ks ^ 1)) * 8 + wid) * (BN >> 4)) * 128;
+          for (int c = c_begin; c < c_end; c++) {
+            uint32_t const bytes = (uint32_t)(min(64, BN - c * 64) >> 4) * 2048u;
+            mbar_expect_tx(&part_bar[q][c], bytes);
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(smem_u32(part + (size_t)c * 8192)), "l"(src + (size_t)c * 512), "r"(bytes),
+                           "r"(smem_u32(&part_bar[q][c])) : "memory");
+          }
+        }
+        __syncwarp();
+      }
+      // 64-column chunks: TMEM -> registers (+ bias, convert) -> this warp's 32 x 128 B staging tile (16-byte units
+      // XOR-swizzled by row, conflict-free both ways) -> global with 8 lanes per row, so that every warp store
+      // covers 4 full 128-byte lines (a thread-per-row store touches 32 lines per instruction and made the
+      // epilogue LSU-bound: 2.4 us per 256-column tile).  The tcgen05.ld of chunk c + 1 is in flight during the
+      // read-back of chunk c.  Columns past BN / N are loaded (inside the 256-column buffer) but never stored.
+      int const col0 = n_blk * BN, row0 = row - lane;
+      uint8_t *const stg = stage_out + (warp - 4) * 4096;
+      uint32_t ra[32], rb[32];
+      if (c_begin < c_end) {
+        tmem_ld32_nowait(tsrc + (uint32_t)(c_begin * 64), ra);
+        tmem_ld32_nowait(tsrc + (uint32_t)(c_begin * 64 + 32), rb);
+      }
+#pragma unroll 1
+      for (int c0 = c_begin * 64; c0 < c_end * 64; c0 += 64) {
+        tmem_ld_wait32(ra);
+        reg_tie32(rb);
+        if (S == 2) {
+          mbar_wait(&part_bar[q][c0 >> 6], 0);
+          float4 const *p4 = reinterpret_cast<float4 const *>(part + (size_t)(c0 >> 6) * 8192) + lane;
+#pragma unroll
+          for (int j = 0; j < 16; j++) {
+            if (c0 + j * 4 < BN) {
+              float4 const a = p4[j * 32];
+              uint32_t *r = j < 8 ? &ra[j * 4] : &rb[(j - 8) * 4];
+              r[0] = __float_as_uint(__uint_as_float(r[0]) + a.x);
+              r[1] = __float_as_uint(__uint_as_float(r[1]) + a.y);
+              r[2] = __float_as_uint(__uint_as_float(r[2]) + a.z);
+              r[3] = __float_as_uint(__uint_as_float(r[3]) + a.w);
+            }
+          }
+        }
+        T const *const bp = bias ? bias + col0 + c0 : nullptr;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+          float f[8];
+#pragma unroll
+          for (int e = 0; e < 8; e++) {
+            f[e] = __uint_as_float(j < 4 ? ra[j * 8 + e] : rb[(j - 4) * 8 + e]);
+          }
+          if (bp && col0 + c0 + j * 8 < N && c0 + j * 8 < BN) {
+#pragma unroll
+            for (int e = 0; e < 8; e++) {
+              f[e] += DT<T>::to_f(bp[j * 8 + e]);
+            }
+          }
+          *reinterpret_cast<uint4 *>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) = pack8<T>(f);
+        }
+        if (c0 + 64 < c_end * 64) {
+          tmem_ld32_nowait(tsrc + (uint32_t)(c0 + 64), ra);
+          tmem_ld32_nowait(tsrc + (uint32_t)(c0 + 96), rb);
+        }
+        __syncwarp();
+        int const j = lane & 7, gcol = col0 + c0 + j * 8;
+        bool const col_ok = gcol < N && c0 + j * 8 < BN;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+          int const r = i * 4 + (lane >> 3);
+          uint4 const v = *reinterpret_cast<uint4 const *>(stg + r * 128 + ((j ^ (r & 7)) << 4));
+          if (col_ok && row0 + r < M) {
+            *reinterpret_cast<uint4 *>(out + (size_t)(row0 + r) * N + gcol) = v;
+          }
+        }
+        __syncwarp();
+      }
+      if (warp == 4 && lane == 0) {
+        T2_TR(6);
       }
       // hand the buffer back to the leader's MMA issuer
       tc_fence_before();
@@ -198,18 +376,30 @@ linear_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
   }
   tc_fence_before();
-  cluster_sync_all(); // neither CTA frees tensor memory / exits while the peer may still use its smem or TMEM
+  // neither CTA frees tensor memory / exits while the peer may still use its smem or TMEM; execution ordering only
+  // (a .release arrive would wait for this thread's global stores to drain: 1 us)
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
   if (warp == 2) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u));
   }
+#ifdef FFB_TC2_TRACE_BUILD
+  if (threadIdx.x == 0) {
+    T2_TR(7);
+    if (blockIdx.x == 0) {
+      __threadfence();
+      g_tc2_launch = g_tc2_launch + 1;
+    }
+  }
+#endif
 }
 
 template <typename T>
 int launch_one(void const *in, void *out, void const *w, void const *bias, int dtype, int M, int K, int N, int BN,
-               cudaStream_t s) {
+               int S, void *ws, int *cnt, cudaStream_t s) {
   size_t const stage = (size_t)(T2_BM + BN / 2) * T2_BK * 2;
-  int const stages = std::min<int>(T2_MAX_STAGES, (int)(((size_t)196 << 10) / stage));
+  int const stages = std::min<int>(T2_MAX_STAGES, (int)(((size_t)208 << 10) / stage));
   CUtensorMap tmA, tmB;
   int rc = make_tensor_map_2d(&tmA, dtype, in, M, K, T2_BM);
   if (rc != FFB_OK) {
@@ -221,14 +411,32 @@ int launch_one(void const *in, void *out, void const *w, void const *bias, int d
   }
   static bool attr_set = false;
   if (!attr_set) {
-    FFB_CUDA_TRY(cudaFuncSetAttribute(linear_tc2_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(((size_t)197 << 10) + 1024)));
+    FFB_CUDA_TRY(cudaFuncSetAttribute(linear_tc2_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(((size_t)225 << 10) + 1024)));
     attr_set = true;
   }
-  size_t const smem = (size_t)stages * stage + 1024;
+  size_t const smem = (size_t)stages * stage + 16384 + 1024; // ring + epilogue staging + alignment slack
   int const tiles = ((N + BN - 1) / BN) * ((M + 255) / 256);
-  dim3 grid(2 * std::min(tiles, kNumSMs / 2));
-  linear_tc2_kernel<T><<<grid, T2_THREADS, smem, s>>>(tmA, tmB, (T *)out, (T const *)bias, M, N, K, BN, stages);
+  dim3 grid(2 * std::min(tiles * S, kNumSMs / 2));
+  linear_tc2_kernel<T><<<grid, T2_THREADS, smem, s>>>(tmA, tmB, (T *)out, (T const *)bias, M, N, K, BN, stages, S,
+                                                      (float4 *)ws, cnt);
   FFB_LAUNCH_CHECK();
+#ifdef FFB_TC2_TRACE_BUILD
+  static int calls = 0;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(s, &cap);
+  if (getenv("FFB_TC2_TRACE") && cap == cudaStreamCaptureStatusNone && ++calls % 8 == 0) {
+    long long host[8][16];
+    cudaStreamSynchronize(s);
+    cudaMemcpyFromSymbol(host, g_tc2_trace, sizeof(host));
+    for (int r = 0; r < 8; r++) {
+      fprintf(stderr, "TC2TRACE M %d K %d N %d BN %d S %d:", M, K, N, BN, S);
+      for (int e = 0; e < 8; e++) {
+        fprintf(stderr, " %lld", host[r][e] - host[0][0]);
+      }
+      fprintf(stderr, "\n");
+    }
+  }
+#endif
   return FFB_OK;
 }
 
@@ -241,24 +449,43 @@ int linear_tc2_supported(int dtype, int M, int K, int N) {
   return (dtype == FFB_DT_HALF || dtype == FFB_DT_BF16) && M > 0 && K % T2_BK == 0 && N % 16 == 0;
 }
 
-// w: dense [N][K] DT weights (already dequantised for quantised layers)
+// split-K workspace: one 256 x 256 fp32 partial per SM pair (S > 1 only when all units fit one wave) + one arrival
+// counter per (tile, epilogue warp)
+size_t linear_tc2_ws_bytes() { return (size_t)(kNumSMs / 2) * 256 * 256 * 4; }
+size_t linear_tc2_cnt_bytes() { return (size_t)(kNumSMs / 2) * 8 * sizeof(int); }
+
+// w: dense [N][K] DT weights (already dequantised for quantised layers); ws / cnt: split-K workspace (or null)
 int launch_linear_tc2(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N,
-                      cudaStream_t s) {
-  // Tile width.  The kernel is bound by the L2 -> SM fabric (~6300 B/cycle chip-wide, B300_MICROARCH.md): with all
-  // 74 SM pairs busy a tile costs ~(256 + BN) operand rows per k-block, and a pair running alone is only ~12 %
-  // faster (measured), so a wave of `a` tiles costs (256 + BN) * max(a / 74, 0.885).  Pick the multiple of 16 that
-  // minimises the sum over waves - e.g. 168 for M = 512, N = 12288 (2 x 74 tiles = exactly two full waves).
-  int const pairs = kNumSMs / 2;
+                      void *ws, int *cnt, cudaStream_t s) {
+  // Tile width and k-split.  The kernel is bound by the L2 -> SM fabric (~6300 B/cycle chip-wide,
+  // B300_MICROARCH.md): with all 74 SM pairs busy a tile costs ~(256 + BN) operand rows per k-block, and a pair
+  // running alone is only ~12 % faster (measured), so a wave of `a` units costs (256 + BN) / S * max(a / 74, 0.885).
+  // Pick the (multiple of 16, S) that minimises the sum over waves - e.g. BN = 168 for M = 512, N = 12288 (2 x 74
+  // tiles = exactly two full waves), BN = 256 with S = 2 for M = 512, N = 4096 (64 units in one wave instead of
+  // 32 tiles on 74 pairs).  S > 1 pays a merge (fp32 partials through L2) and must fit one wave.
+  int const pairs = kNumSMs / 2, num_k = K / T2_BK;
   long const mt = (M + 255) / 256;
-  int bn = 128;
+  int bn = 128, split = 1;
   double best = -1.0;
-  for (int c = 64; c <= 256; c += 16) {
-    long const tiles = mt * ((N + c - 1) / c);
-    long const full = tiles / pairs, rem = tiles % pairs;
-    double const cost = (256.0 + c) * ((double)full + (rem ? std::max((double)rem / pairs, 0.885) : 0.0));
-    if (best < 0 || cost < best - 1e-9) {
-      best = cost;
-      bn = c;
+  static double const merge_cost = getenv("FFB_TC2_MERGE_COST") ? atof(getenv("FFB_TC2_MERGE_COST")) : 64.0;
+  for (int S = 1; S <= (ws && cnt ? 2 : 1); S++) {
+    if (S > 1 && num_k / S < 8) {
+      break;
+    }
+    for (int c = 64; c <= 256; c += 16) {
+      long const tiles = mt * ((N + c - 1) / c);
+      long const units = tiles * S;
+      if (S > 1 && units > pairs) {
+        continue;
+      }
+      long const full = units / pairs, rem = units % pairs;
+      double const cost = (256.0 + c) / S * ((double)full + (rem ? std::max((double)rem / pairs, 0.885) : 0.0)) +
+                          (S > 1 ? merge_cost : 0.0);
+      if (best < 0 || cost < best - 1e-9) {
+        best = cost;
+        bn = c;
+        split = S;
+      }
     }
   }
   if (char const *e = getenv("FFB_TC2_BN")) {
@@ -267,10 +494,19 @@ int launch_linear_tc2(int dtype, void const *in, void *out, void const *w, void 
       bn = v;
     }
   }
-  if (dtype == FFB_DT_HALF) {
-    return launch_one<__half>(in, out, w, bias, dtype, M, K, N, bn, s);
+  if (char const *e = getenv("FFB_TC2_SPLIT")) {
+    int v = atoi(e);
+    if (v >= 1 && v <= 2 && (v == 1 || (ws && cnt))) { // S - 1 partials of 512 x BN bytes live in the idle ring
+      split = v;
+    }
   }
-  return launch_one<__nv_bfloat16>(in, out, w, bias, dtype, M, K, N, bn, s);
+  if (split > 1 && (mt * ((N + bn - 1) / bn) * split > pairs || num_k < split)) {
+    split = 1; // (env overrides) the workspace holds one wave of units
+  }
+  if (dtype == FFB_DT_HALF) {
+    return launch_one<__half>(in, out, w, bias, dtype, M, K, N, bn, split, ws, cnt, s);
+  }
+  return launch_one<__nv_bfloat16>(in, out, w, bias, dtype, M, K, N, bn, split, ws, cnt, s);
 }
 
 } // namespace ffb

@@ -57,6 +57,40 @@ def test_linear_tc2_pair_tiles(M, K, N, bn, monkeypatch):
     assert np.abs(got - want).max() <= 2e-3 * max(1.0, np.abs(want).max())
 
 
+@pytest.mark.parametrize("split", ["2", "auto"])
+@pytest.mark.parametrize("M,K,N,bias", [(512, 4096, 1024, True), (300, 2048, 768, False), (200, 1024, 1248, True),
+                                        (512, 4096, 4096, False)])
+def test_linear_tc2_split_k(M, K, N, bias, split, monkeypatch):
+    """Split-K SM-pair GEMM (the second k-slice parks its fp32 partial in the L2 workspace, the tile's owner bulk-copies
+    it into its idle operand ring and adds it), called three times on one handle: the arrival counters must come back
+    to zero and the result must not depend on timing."""
+    import torch
+    from flexflow_b200 import ops
+    monkeypatch.setenv("FFB_LINEAR", "tc")
+    if split != "auto":
+        monkeypatch.setenv("FFB_TC2_SPLIT", split)
+        monkeypatch.setenv("FFB_TC2_BN", "256" if N >= 1024 else "128")
+    rng = np.random.default_rng(35)
+    x = O.round_to_dt(rng.standard_normal((M, K)).astype(np.float32), "half")
+    w = O.round_to_dt((rng.standard_normal((N, K)) * 0.05).astype(np.float32), "half")
+    b = O.round_to_dt(rng.standard_normal(N).astype(np.float32), "half") if bias else None
+    h = ops.FFHandler("cuda:0")
+    m = ops.LinearMeta(h, K, N, dtype=torch.float16, max_tokens_per_batch=1024)
+    xd, wd = torch.from_numpy(x).cuda().half(), torch.from_numpy(w).cuda().half()
+    bd = torch.from_numpy(b).cuda().half() if bias else None
+    outs = []
+    for _ in range(3):
+        out = torch.full((M, N), float("nan"), dtype=torch.float16, device="cuda")
+        ops.Linear.inference_kernel_wrapper(m, None, xd, out, wd, bd, K, N, M)
+        outs.append(out)
+    torch.cuda.synchronize()
+    want = O.linear(x, w, b, "half")
+    got = outs[0].float().cpu().numpy()
+    assert np.isfinite(got).all()
+    assert np.abs(got - want).max() <= 2e-3 * max(1.0, np.abs(want).max())
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+
+
 @pytest.mark.parametrize("quant", [8, 4])
 def test_linear_tc_quantised_matches_stream(quant, monkeypatch):
     """Large-M quantised path (dequant scratch + tcgen05 GEMM) against the oracle on the dequantised weights."""
