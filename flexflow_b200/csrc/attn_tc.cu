@@ -61,8 +61,9 @@ template <int DH> struct AtcCfg {
   static constexpr int KH = DH / 64;                    // 64-element (128-byte) column blocks per row
   static constexpr uint32_t HALF_BYTES = 128 * 128;     // one [128 keys][64 cols] swizzled block
   static constexpr uint32_t KV_BYTES = KH * HALF_BYTES; // one K tile or one V tile
-  static constexpr int NBUF = (192 * 1024) / KV_BYTES;  // ring slots; K and V tiles alternate: K0 V0 K1 V1 ...
-  static constexpr size_t SMEM = (size_t)NBUF * KV_BYTES + 1024;
+  static constexpr int NBUF = (160 * 1024) / KV_BYTES;  // ring slots; K and V tiles alternate: K0 V0 K1 V1 ...
+  static constexpr uint32_t Q_BYTES = 128 * DH * 2;      // next segment's Q rows, staged by cp.async
+  static constexpr size_t SMEM = (size_t)NBUF * KV_BYTES + Q_BYTES + 16384 + 1024; // ring + Q + output staging + alignment
 };
 
 // Walks the segments of one CTA: maximal runs of consecutive flattened tiles inside one unit.
@@ -97,7 +98,7 @@ template <typename T, int DH>
 // 10 warps are allocated as 12 (warp allocation granularity 4): 65536 / 384 = 170 registers per thread at most
 __global__ void __launch_bounds__(ATC_THREADS, 1)
 attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
-               const __grid_constant__ AtcSched sched, T const *__restrict__ q_buf,
+               const __grid_constant__ AtcSched sched_param, T const *__restrict__ q_buf,
                QueryDesc const *__restrict__ qdesc, ffb_combined_batch_config_meta const *__restrict__ meta,
                float *__restrict__ partial, int *__restrict__ split_counter, T *__restrict__ out, int nq, int nkv,
                int cache_len, float scale_log2, long long *trace) {
@@ -110,7 +111,9 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
   __shared__ float s_xch[2][2][TBM]; // [tile parity][column half][row]: partial row maxima / final row sums
   __shared__ uint32_t tmem_base_smem;
   __shared__ int s_rowlast[TBM];
-  __shared__ unsigned long long s_mask[2][64]; // tree bit masks of the current / next segment's request
+  // tree bit masks of the current / next segment's request, TRANSPOSED: bit i of s_maskT[.][b] = bit b of mask[i]
+  __shared__ unsigned long long s_maskT[2][64];
+  __shared__ AtcSched s_sched;
 
   int const tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   int const G = nq / nkv;
@@ -128,11 +131,35 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
     }
   };
 #define FFB_TR(role, ev) tr(role, ev)
+  if (trace && tid == 0) { // every CTA: start / end stamps and the SM it ran on, in trace[1536 + 3 * cta ...]
+    long long t;
+    unsigned smid;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    trace[1536 + 3 * blockIdx.x] = t;
+    trace[1536 + 3 * blockIdx.x + 2] = smid;
+  }
 #else
 #define FFB_TR(role, ev) ((void)0)
 #endif
   // 128B-swizzled operand blocks need 1024-byte alignment
   uint8_t *sKV = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t *const sQ = sKV + (size_t)NBUF * Cfg::KV_BYTES;     // [128 rows][DH] of the NEXT segment's Q
+  uint8_t *const sStage = sQ + Cfg::Q_BYTES;                  // 8 softmax warps x 2 KB output staging
+
+  // The tile schedule is walked by all three roles at every unit boundary.  In parameter (constant) space each
+  // first touch of a line is a ~0.7 us miss and the walks are dependent chains (2 us per boundary, measured): copy
+  // the entries in use to shared memory once.
+  {
+    int const *src = reinterpret_cast<int const *>(&sched_param);
+    int *dst = reinterpret_cast<int *>(&s_sched);
+    int const words = 4 + sched_param.n_ent * (int)(sizeof(AtcEntry) / 4);
+    for (int i = tid; i < words; i += ATC_THREADS) {
+      dst[i] = src[i];
+    }
+  }
+  __syncthreads();
+  AtcSched const &sched = s_sched;
 
   if (warp == 8) {
     // ===== TMA producer =====  (never waits for the rest of the CTA: the stream starts at once)
@@ -274,7 +301,18 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
           QueryDesc const qd = qdesc[tok];
           n_kvl = qd.kv_len;
           n_bit = qd.bit;
+          // this thread's half row of Q -> shared memory, asynchronously (no registers held while the current
+          // segment streams; under load an L2 round trip at the unit boundary costs 2-3 us).  16-byte units are
+          // XOR-swizzled by row so that the read-back at publish time is conflict-free.
+          uint32_t const dst = smem_u32(sQ) + (uint32_t)row * (DH * 2) + (uint32_t)hc * DH;
+          T const *src = q_buf + (size_t)n_th * DH + hc * (DH / 2);
+#pragma unroll
+          for (int c = 0; c < QW / 4; c++) {
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + (uint32_t)((c ^ (row & (QW / 4 - 1))) << 4)),
+                         "l"(src + c * 8) : "memory");
+          }
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
         if (hc == 1 && row < 64) {
           n_mask = meta->causalMask[en.slot].mask[row];
         }
@@ -283,10 +321,12 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
       // row tables -> shared-memory buffer `tb`
       auto publish_rows = [&](int tb) {
         uint32_t n_q[32];
-        uint4 const *src = reinterpret_cast<uint4 const *>(q_buf + (size_t)(n_th >= 0 ? n_th : 0) * DH + hc * (DH / 2));
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        uint8_t const *src = sQ + (size_t)row * (DH * 2) + hc * DH;
 #pragma unroll
-        for (int c = 0; c < QW / 4; c++) { // q_buf was written by the prep kernel just before: L2 hits
-          uint4 const v = n_th >= 0 ? src[c] : make_uint4(0u, 0u, 0u, 0u);
+        for (int c = 0; c < QW / 4; c++) {
+          uint4 const v = n_th >= 0 ? *reinterpret_cast<uint4 const *>(src + ((c ^ (row & (QW / 4 - 1))) << 4))
+                                    : make_uint4(0u, 0u, 0u, 0u);
           n_q[c * 4 + 0] = v.x; n_q[c * 4 + 1] = v.y; n_q[c * 4 + 2] = v.z; n_q[c * 4 + 3] = v.w;
         }
         if (DH == 128) {
@@ -295,22 +335,40 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
           tmem_st16(tq, n_q);
         }
         tmem_st_wait();
+        if (hc == 1 && row < 64) {
+          // warps 4 and 5 hold mask[0..31] / mask[32..63], one word per lane: 64 ballots transpose them (lane l keeps
+          // the words of bits l and l + 32); the two warps write the low / high halves of the transposed words
+          uint32_t keep0 = 0, keep1 = 0;
+#pragma unroll 8
+          for (int bb = 0; bb < 32; bb++) {
+            uint32_t const b0 = __ballot_sync(0xffffffffu, (n_mask >> bb) & 1ULL);
+            uint32_t const b1 = __ballot_sync(0xffffffffu, (n_mask >> (bb + 32)) & 1ULL);
+            if ((row & 31) == bb) {
+              keep0 = b0;
+              keep1 = b1;
+            }
+          }
+          uint32_t *const dstw = reinterpret_cast<uint32_t *>(&s_maskT[tb][0]) + (row >> 5);
+          dstw[2 * (row & 31)] = keep0;
+          dstw[2 * ((row & 31) + 32)] = keep1;
+        }
+        // (release) the first QK^T of the segment is issued after all 256 arrivals, and every softmax thread reads
+        // s_maskT[tb] only after that MMA's s_full: no CTA-wide barrier at the unit boundary
         tc_fence_before();
         mbar_arrive(&q_full);
-        if (hc == 1 && row < 64) {
-          s_mask[tb][row] = n_mask;
-        }
       };
 
       SegWalk w;
       w.init(sched);
       bool have = w.next(sched);
       int g0 = 0, tb = 0;
+      if (tid == 0) FFB_TR(2, 100);
       if (have) {
         fetch_rows(w);
+        if (tid == 0) FFB_TR(2, 101);
         publish_rows(0);
       }
-      asm volatile("bar.sync 5, 256;" ::: "memory");
+      if (tid == 0) FFB_TR(2, 102);
       while (have) {
         AtcEntry const &en = sched.ent[w.e];
         int const ntiles = w.t1 - w.t0, ntcs = en.ntcs, t_first = w.t0;
@@ -320,24 +378,17 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
         int const piece = (int)blockIdx.x - c_first;
         int const th = n_th, kvl = n_kvl, bit = n_bit;
         bool const warp_active = __any_sync(0xffffffffu, th >= 0); // padding-only warps just keep the barriers moving
+        if (tid == 0) FFB_TR(2, 105);
         have = w.next(sched);
+        if (tid == 0) FFB_TR(2, 106 + (have ? 0 : 1));
         if (have) {
           fetch_rows(w); // next segment's rows: loads stay in flight while this segment streams
         }
+        if (tid == 0) FFB_TR(2, 104);
         float m_ref = -INFINITY, l = 0.f;
         // tree / beam rows: bit i of row_vis says whether tree position i (key ntcs + i) is visible to this row
         // (mask rule tree_…cu:165-169 / spec_…cu:165-167 with 1ULL semantics), transposed once per segment
         unsigned long long row_vis = 0;
-        if (__any_sync(0xffffffffu, bit >= 0 && bit < 64)) {
-          int const sb = bit & 63;
-#pragma unroll 8
-          for (int i = 0; i < 64; i++) {
-            row_vis |= ((s_mask[tb][i] >> sb) & 1ULL) << i;
-          }
-          if (bit < 0 || bit >= 64) {
-            row_vis = 0;
-          }
-        }
 
         for (int it = 0; it < ntiles; it++) {
           int const g = g0 + it, b = g & 1;
@@ -349,6 +400,9 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
           mbar_wait(&s_full[b], (g >> 1) & 1);
           if (tid == 0) FFB_TR(2, 2000 + g);
           tc_fence_after();
+          if (it == 0 && bit >= 0 && bit < 64) {
+            row_vis = s_maskT[tb][bit];
+          }
           float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
           if (warp_active) {
             uint32_t r0[32], r1[32];
@@ -464,28 +518,42 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
         if (tid == 0) FFB_TR(2, 4000);
         s_xch[0][hc][row] = l;
         mbar_wait(&o_full, g_last & 1);
+        if (tid == 0) FFB_TR(2, 4010);
         tc_fence_after();
         asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+        if (tid == 0) FFB_TR(2, 4020);
         l += s_xch[0][hc ^ 1][row];
         if (npieces == 1) {
           if (warp_active) {
+            // TMEM -> registers (x 1/sum, convert) -> this warp's 32 x 64 B staging tile (16-byte units XOR-swizzled
+            // by row pair: conflict-free both ways) -> global with 4 lanes per row, so that a warp store covers
+            // 8 rows x 64 contiguous bytes (a thread-per-row store touches 32 lines per instruction: LSU-bound)
             float const inv = __fdividef(1.f, l + 1.e-6f);
-            uint4 *dst = reinterpret_cast<uint4 *>(out + (size_t)(th >= 0 ? th : 0) * DH + hc * OC);
+            uint8_t *const stg = sStage + warp * 2048;
 #pragma unroll
             for (int c = 0; c < OC / 32; c++) {
               uint32_t r[32];
               tmem_ld32(tO + (uint32_t)(c * 32), r);
-              if (th >= 0) {
 #pragma unroll
-                for (int v4 = 0; v4 < 4; v4++) {
-                  float f[8];
+              for (int v4 = 0; v4 < 4; v4++) {
+                float f[8];
 #pragma unroll
-                  for (int e = 0; e < 8; e++) {
-                    f[e] = __uint_as_float(r[v4 * 8 + e]) * inv;
-                  }
-                  dst[c * 4 + v4] = pack8<T>(f);
+                for (int e = 0; e < 8; e++) {
+                  f[e] = __uint_as_float(r[v4 * 8 + e]) * inv;
+                }
+                *reinterpret_cast<uint4 *>(stg + lane * 64 + ((v4 ^ ((lane >> 1) & 3)) << 4)) = pack8<T>(f);
+              }
+              __syncwarp();
+#pragma unroll
+              for (int i = 0; i < 4; i++) {
+                int const rr = i * 8 + (lane >> 2), j = lane & 3;
+                uint4 const v = *reinterpret_cast<uint4 const *>(stg + rr * 64 + ((j ^ ((rr >> 1) & 3)) << 4));
+                int const thr = __shfl_sync(0xffffffffu, th, rr);
+                if (thr >= 0) {
+                  *reinterpret_cast<uint4 *>(out + (size_t)thr * DH + hc * OC + c * 32 + j * 8) = v;
                 }
               }
+              __syncwarp();
             }
           }
         } else {
@@ -495,7 +563,64 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
           // segment), slot 2c when the unit ends there (its first segment).
           constexpr int SLOT = (DH + 2) * TBM;
           if (tid == 0) FFB_TR(2, 4050);
-          if (warp_active) {
+          // Fast path.  Piece 0 of a unit is its CTA's LAST segment, piece 1 (of two) its CTA's FIRST: piece 1's record
+          // has nearly always landed by now.  If so (per row), merge straight from tensor memory: no record, no
+          // fence, no atomic, one round trip to L2 instead of four.  mode: 0 = general path, 2 = fast, 3 = idle row.
+          int mode = 0;
+          if (piece == 0 && npieces == 2) {
+            if (hc == 0) {
+              // the decision is per WARP (32 rows; the tcgen05.ld below needs the warp converged)
+              int seen = 1;
+              if (th >= 0) {
+                asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(split_counter + th) : "memory");
+              }
+              int const f = __all_sync(0xffffffffu, seen == 1) ? (th >= 0 ? 2 : 3) : 0;
+              if (f == 2) {
+                split_counter[th] = 0;
+              }
+              s_rowlast[row] = f;
+            }
+            asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+            mode = s_rowlast[row];
+          }
+          if (mode != 0 && warp_active) {
+            __threadfence();
+            // (idle rows read their - unused - record row too: the loads stay unconditional and batched)
+            float const *rs = partial + row + (size_t)(2 * (c_first + 1)) * SLOT;
+            float const mb = __ldcg(rs + DH * TBM), lb = __ldcg(rs + (DH + 1) * TBM);
+            float vb[OC];
+#pragma unroll
+            for (int d = 0; d < OC; d++) {
+              vb[d] = __ldcg(rs + (hc * OC + d) * TBM);
+            }
+            // same operations in the same order as the general merge below: bit-identical whichever path runs
+            float M = -INFINITY, L = 0.f;
+            M = fmaxf(M, m_ref);
+            M = fmaxf(M, mb);
+            float const wa = m_ref == -INFINITY ? 0.f : ffb_ex2(m_ref - M);
+            float const wb = mb == -INFINITY ? 0.f : ffb_ex2(mb - M);
+            L += l * wa;
+            L += lb * wb;
+            float const inv = __fdividef(1.f, L + 1.e-6f);
+            uint4 *dst = reinterpret_cast<uint4 *>(out + (size_t)(th >= 0 ? th : 0) * DH + hc * OC);
+#pragma unroll
+            for (int c = 0; c < OC / 32; c++) {
+              uint32_t r[32];
+              tmem_ld32(tO + (uint32_t)(c * 32), r);
+              if (mode == 2) {
+#pragma unroll
+                for (int v4 = 0; v4 < 4; v4++) {
+                  float f[8];
+#pragma unroll
+                  for (int e = 0; e < 8; e++) {
+                    f[e] = fmaf(__uint_as_float(r[v4 * 8 + e]), wa, fmaf(vb[c * 32 + v4 * 8 + e], wb, 0.f)) * inv;
+                  }
+                  dst[c * 4 + v4] = pack8<T>(f);
+                }
+              }
+            }
+          }
+          if (mode == 0 && warp_active) {
             float *rec = partial + (size_t)(2 * (int)blockIdx.x + (piece < npieces - 1 ? 1 : 0)) * SLOT + row;
 #pragma unroll
             for (int c = 0; c < OC / 32; c++) {
@@ -515,10 +640,12 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
           // of the row merge their own half of the columns (exact log-sum-exp merge, then the reference's
           // 1/(sum + 1e-6), inc_…cu:538)
           if (tid == 0) FFB_TR(2, 4100);
-          __threadfence();
+          if (mode == 0) {
+            __threadfence();
+          }
           if (tid == 0) FFB_TR(2, 4200);
           asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
-          if (hc == 0) {
+          if (hc == 0 && mode == 0) {
             int last = 0;
             if (th >= 0) {
               int const prev = atomicAdd(&split_counter[th], 1);
@@ -531,7 +658,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
           }
           asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
           if (tid == 0) FFB_TR(2, 4300 + s_rowlast[row]);
-          if (s_rowlast[row]) {
+          if (mode == 0 && s_rowlast[row]) {
             __threadfence();
             float const *rec0 = partial + row;
             auto slot_of = [&](int i) { return rec0 + (size_t)(2 * (c_first + i) + (i < npieces - 1 ? 1 : 0)) * SLOT; };
@@ -585,7 +712,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
           }
         }
         if (tid == 0) FFB_TR(2, 5000);
-        asm volatile("bar.sync 5, 256;" ::: "memory"); // next segment's tables are published, this one's are free
+        // (s_maskT is double-buffered: buffer tb is rewritten at the end of the NEXT segment, by which time every
+        // warp - none can run a tile ahead of the p_full / o_full handshakes - has read it)
         tb ^= 1;
         g0 += ntiles;
       }
@@ -599,6 +727,13 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
     __syncwarp();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base_smem), "r"(512u));
   }
+#ifdef FFB_ATC_TRACE_BUILD
+  if (trace && tid == 0) {
+    long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    trace[1536 + 3 * blockIdx.x + 1] = t;
+  }
+#endif
 }
 
 } // namespace
@@ -717,10 +852,10 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
   static int trace_calls = 0;
   bool const tracing = getenv("FFB_ATC_TRACE") != nullptr;
   if (tracing && !trace) {
-    cudaMalloc(&trace, 3 * 512 * sizeof(long long));
+    cudaMalloc(&trace, (3 * 512 + 3 * 160) * sizeof(long long));
   }
   if (tracing) {
-    cudaMemsetAsync(trace, 0, 3 * 512 * sizeof(long long), s);
+    cudaMemsetAsync(trace, 0, (3 * 512 + 3 * 160) * sizeof(long long), s);
   }
   CUtensorMap const &tmK = *reinterpret_cast<CUtensorMap const *>(h->tmK);
   CUtensorMap const &tmV = *reinterpret_cast<CUtensorMap const *>(h->tmV);
@@ -750,7 +885,7 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
   }
   FFB_LAUNCH_CHECK();
   if (tracing && ++trace_calls == atoi(getenv("FFB_ATC_TRACE"))) { // dump the n-th launch
-    static long long host[3 * 512];
+    static long long host[3 * 512 + 3 * 160];
     cudaStreamSynchronize(s);
     cudaMemcpy(host, trace, sizeof(host), cudaMemcpyDeviceToHost);
     long long t0 = host[1];
@@ -758,6 +893,10 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
       for (int i = 0; i < 255 && host[r * 512 + 2 * i + 1]; i++) {
         fprintf(stderr, "TRACE role %d ev %lld t %lld\n", r, host[r * 512 + 2 * i], host[r * 512 + 2 * i + 1] - t0);
       }
+    }
+    for (int c = 0; c < grid; c++) {
+      fprintf(stderr, "TRACE cta %d sm %lld start %lld end %lld\n", c, host[1536 + 3 * c + 2], host[1536 + 3 * c] - t0,
+              host[1536 + 3 * c + 1] - t0);
     }
     fprintf(stderr, "TRACE grid %d rg %d maxp %d total %d\n", grid, rg, maxp, cum);
   }
