@@ -24,6 +24,7 @@ SOURCES = [
     "linear_tc2.cu",
     "capi_linear.cu",
     "comm.cu",
+    "host_tree.cu",
 ]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -64,6 +64,11 @@ SIGNATURES = {
     "ffb_allreduce": (_i, [_vp, _vp, _vp, _sz, _i, _vp]),
     "ffb_comm_has_peer": (_i, [_vp]),
     "ffb_linear_forward_allreduce": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
+    "ffb_bitmask_init": (None, [_vp, _i]),
+    "ffb_bitmask_update": (None, [_vp, _i, _i]),
+    "ffb_bitmask_append_pending": (None, [_vp, _i]),
+    "ffb_bitmask_append": (_i, [_vp, _i, _vp, _i]),
+    "ffb_traverse_verify_tree": (_i, [_vp, _i, _vp, _i, _vp, _vp, C.POINTER(_i), _vp, C.POINTER(_i)]),
 }
 
 _lib = None

@@ -183,6 +183,37 @@ int ffb_comm_has_peer(ffb_comm_t c);
 int ffb_linear_forward_allreduce(ffb_linear_t h, ffb_comm_t comm, void const *in_dev, void *out_dev,
                                  void const *weight_dev, void const *bias_dev, int batch, ffb_stream_t stream);
 
+/* ---- host-side SpecInfer tree logic (integer only; runs on the host, no CUDA call) ---------------------------------
+ * The bit masks these build are what ffb_tree_attn_forward / ffb_spec_attn_forward read from causalMask[], and
+ * ffb_traverse_verify_tree turns the LLM's per-node outputs into the accepted tokens and the commit list of the next
+ * verify batch.  Replaces RequestManager::{initBitMask, updateBitMask, appendPendingRequest, appendBitMask,
+ * traverse_verify_tree} (src/runtime/request_manager.cc:2382-2396, 2399-2427, 2430-2446, 2448-2517, 2583-2741).
+ * Bits are set with 64-bit shifts (the reference's `1 << j` is a 32-bit shift, identical up to tree index 30). */
+void ffb_bitmask_init(ffb_bit_mask *bm, int init_length);
+void ffb_bitmask_update(ffb_bit_mask *bm, int init_length, int non_tree_size);
+void ffb_bitmask_append_pending(ffb_bit_mask *bm, int init_length);
+/* new_nodes = nodes of the new (deepest) layer; layer_nodes[i] = treeLayers[i].nodes_num_this_layer for
+ * i < current_depth.  FFB_ERR_INVALID when the tree would exceed FFB_MAX_SPEC_TREE_TOKEN_NUM nodes (the reference
+ * asserts), FFB_ERR_STATE when the layer widths do not add up to the nodes already in the mask. */
+int ffb_bitmask_append(ffb_bit_mask *bm, int new_nodes, int const *layer_nodes, int current_depth);
+
+typedef struct {
+  int token_id;
+  int depth; /* absolute position in the request's sequence */
+} ffb_tree_node;
+typedef struct {
+  int depth;
+  int index_in_batch;
+} ffb_commit_entry;
+/* input_tree: the speculated tree serialised in layer order (dfs_tree_inputs); llm_outputs[i]: the LLM's token for node
+ * i with depth + 1; committed_in[i]: (depth, index in the verify batch) of node i.  Writes the verified (token, depth)
+ * sequence and the commit list (at most n_in entries each).  Accept rule: node 0 always; node i > 0 iff it equals the
+ * last verified (token, depth) and is the first such node or sits in the same slot of its layer as the first one.
+ * FFB_ERR_INVALID if n_in < n_out, FFB_ERR_STATE if a committed depth disagrees with the tree (reference asserts). */
+int ffb_traverse_verify_tree(ffb_tree_node const *input_tree, int n_in, ffb_tree_node const *llm_outputs, int n_out,
+                             ffb_commit_entry const *committed_in, ffb_tree_node *verified, int *n_verified,
+                             ffb_commit_entry *committed_out, int *n_committed);
+
 #ifdef __cplusplus
 }
 #endif
