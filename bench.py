@@ -262,6 +262,11 @@ def run_ours(args):
                      "kernel_ms": k_ms, "kernel_timing": k_how, "algorithmic_bytes_per_launch": alg,
                      "attn_share_of_step": k_ms * LAYERS / ms_dev},
     }
+    if tp == 1 and not args.no_quantized:
+        try:
+            line["quantized_decode"] = quantized_extra(args, dev, model, step, ms_dev)
+        except Exception as e:  # the headline line must still print
+            line["quantized_decode"] = {"error": repr(e)}
     if not args.no_tree_verify:
         try:
             line["tree_verify"] = tree_verify_extra(args, dev, comm, rank, tp, model, g)
@@ -274,6 +279,88 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def quantized_extra(args, dev, model, step, ms_fp16):
+    """BASELINE.json configs[2]: the headline decode step with the qkv_proj / o_proj weights stored as the
+    reference's int8 / int4 blobs ([values | offsets | scales], groups of 32 along out, fp16 group meta) and
+    dequantised in registers inside the weight-streaming kernel.  Synthetic blobs: uniform random values with one
+    scale / offset so that the weights span [-0.04, 0.04].  The linear metas of the decode model are swapped for
+    quantised ones, the step graph is captured again and timed the same way; restored afterwards."""
+    import torch
+
+    from flexflow_b200 import batch_config as B
+    from flexflow_b200 import ops
+
+    res = {"workload": "same decode step, qkv_proj / o_proj weights as int8 / int4 blobs, tp1", "fp16_ms_per_step": ms_fp16}
+    lins = [l for l in model.layers if l.op_type == "linear"]
+    saved = [(l.meta, l.weight) for l in lins]
+    gq = torch.Generator(device=dev).manual_seed(99)
+    try:
+        for name, qt, bits in (("int8", B.DT_INT8, 8), ("int4", B.DT_INT4, 4)):
+            wbytes = 0
+            for l in lins:
+                K, N = l.inputs[0].dim, l.output.dim
+                nvals = K * N * bits // 8
+                meta = torch.empty(K * N // 32, dtype=torch.float16, device=dev)
+                blob = torch.cat([torch.randint(0, 256, (nvals,), generator=gq, device=dev, dtype=torch.uint8),
+                                  meta.fill_(-0.04).clone().view(torch.uint8),
+                                  meta.fill_((2 ** bits - 1) / 0.08).clone().view(torch.uint8)])
+                assert blob.numel() == ops.quant_blob_bytes(qt, K, N), "blob layout"
+                l.meta = ops.LinearMeta(model.handler, K, N, torch.float16, qt, BATCH)
+                l.weight = blob
+                wbytes += blob.numel()
+            for _ in range(3):
+                out = step()
+            torch.cuda.synchronize()
+            assert torch.isfinite(out.float()).all(), "non-finite quantised output"
+            gr = None
+            if not args.no_graph:
+                gr = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gr):
+                    step()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            for _ in range(3):
+                gr.replay() if gr is not None else step()
+            e0.record()
+            for _ in range(args.steps):
+                gr.replay() if gr is not None else step()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / args.steps
+
+            def lin_only():  # the 64 projection launches alone (weights: 32 distinct layers, no L2 reuse)
+                for l in lins:
+                    ops.Linear.inference_kernel_wrapper(l.meta, None, l.inputs[0].buf, l.output.buf, l.weight, None,
+                                                        l.inputs[0].dim, l.output.dim, BATCH)
+            lin_ms = None
+            try:
+                lg = torch.cuda.CUDAGraph()
+                lin_only()
+                torch.cuda.synchronize()
+                with torch.cuda.graph(lg):
+                    lin_only()
+                lg.replay()
+                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a0.record()
+                for _ in range(5):
+                    lg.replay()
+                a1.record()
+                torch.cuda.synchronize()
+                lin_ms = a0.elapsed_time(a1) / 5
+            except Exception:  # noqa: BLE001
+                torch.cuda.synchronize()
+            res[name] = {"ms_per_step": ms, "tokens_per_s": BATCH / (ms * 1e-3), "weight_bytes_per_step": wbytes,
+                         "speedup_vs_fp16": ms_fp16 / ms}
+            if lin_ms:
+                peak, _ = peaks()
+                res[name].update({"projections_ms_per_step": lin_ms, "weight_stream_gbs": wbytes / (lin_ms * 1e-3) / 1e9,
+                                  "weight_stream_frac_of_hbm_peak": wbytes / (lin_ms * 1e-3) / 1e9 / peak})
+            del gr
+    finally:
+        for l, (m, w) in zip(lins, saved):
+            l.meta, l.weight = m, w
+    return res
 
 
 def tree_verify_extra(args, dev, comm, rank, tp, decode_model, g):
@@ -483,6 +570,7 @@ def main():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-tree-verify", action="store_true")
+    ap.add_argument("--no-quantized", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

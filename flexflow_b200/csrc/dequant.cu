@@ -5,6 +5,8 @@
 // meta loads and a half division each.  Here a thread owns 8 consecutive columns of one group (32 rows):
 // scale/offset are fetched once as 128-bit loads, the reciprocal is taken once per column, and 32 rows
 // are emitted as 128-bit stores.
+#include <type_traits>
+
 #include "dequant.cuh"
 
 namespace ffb {
@@ -30,6 +32,17 @@ dequant_kernel(uint8_t const *__restrict__ blob, T *__restrict__ out, int in_dim
     for (int e = 0; e < 8; e++) {
       coef[e] = dq_coef(ps[e], po[e]);
     }
+    // half: the two-at-a-time rule of dequant.cuh (same bits, no conversion-pipe work per element)
+    [[maybe_unused]] DqPairHalf pc[4];
+    [[maybe_unused]] bool pairs_ok = true;
+    if constexpr (std::is_same<T, __half>::value) {
+      uint32_t const *ow = reinterpret_cast<uint32_t const *>(&uo);
+#pragma unroll
+      for (int e = 0; e < 4; e++) {
+        pc[e] = dq_pair_coef(ps[2 * e], ps[2 * e + 1], ow[e]);
+        pairs_ok = pairs_ok && dq_pair_ok(pc[e]);
+      }
+    }
     for (int r = 0; r < 32; r++) {
       size_t const idx = (size_t)(g * 32 + r) * in_dim + c8 * 8;
       int q[8];
@@ -47,6 +60,17 @@ dequant_kernel(uint8_t const *__restrict__ blob, T *__restrict__ out, int in_dim
         for (int b = 0; b < 4; b++) {
           q[b] = (int)((v.x >> (8 * b)) & 0xFFu);
           q[4 + b] = (int)((v.y >> (8 * b)) & 0xFFu);
+        }
+      }
+      if constexpr (std::is_same<T, __half>::value) {
+        if (pairs_ok) {
+          uint4 res;
+          res.x = dq_pair(kDqMagic | (uint32_t)q[0], kDqMagic | (uint32_t)q[1], pc[0]);
+          res.y = dq_pair(kDqMagic | (uint32_t)q[2], kDqMagic | (uint32_t)q[3], pc[1]);
+          res.z = dq_pair(kDqMagic | (uint32_t)q[4], kDqMagic | (uint32_t)q[5], pc[2]);
+          res.w = dq_pair(kDqMagic | (uint32_t)q[6], kDqMagic | (uint32_t)q[7], pc[3]);
+          *reinterpret_cast<uint4 *>(out + idx) = res;
+          continue;
         }
       }
       T res[8];

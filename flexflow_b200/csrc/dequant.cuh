@@ -47,6 +47,45 @@ __device__ __forceinline__ __half dq_elem(int q, DqCoefHalf const &c) {
   return __hadd(v, c.off);
 }
 
+// ---- two elements at a time, no conversion-pipe work per element (DT = half) -----------------------------------------
+// dq_elem costs I2F + FMUL + F2H + three half compares + HADD per element, and the I2F / F2H conversions run at a
+// quarter of the FP32 rate: the weight-streaming GEMM was conversion-bound at 1.1 TB/s (int8) / 0.6 TB/s (int4).
+// Same roundings, cheaper instructions:
+//   * float(q): m = 0x4B000000 | q is the float 2^23 + q, and fma(rcp, m, -rcp * 2^23) rounds the exact product
+//     rcp * q once - the value FMUL(rcp, float(q)) gives (-rcp * 2^23 is exact: a power-of-two scaling).  Needs a
+//     finite rcp; dq_pair_ok() says so and the callers fall back to dq_elem otherwise (scale = 0, NaN).
+//   * one cvt.rn.f16x2.f32 rounds both quotients, one HADD2 adds both offsets (adjacent in the blob).
+//   * __hdiv's correction step runs only for 0 < |quotient| < 0x008F (8.5e-6).  With q >= 1 that needs
+//     |rcp| < 8.5e-6, i.e. |scale| > 117000: no half is that large (max 65504; scale = inf gives rcp = 0 and the
+//     quotient 0, also outside the range), so the branch is dead for every possible blob.
+//     tests/test_gpu_linear.py::test_dequant_exhaustive_quotients checks every q x every finite non-zero half scale
+//     through this path against the oracle's IEEE division.
+struct DqPairHalf {
+  float r0, c0, r1, c1; // rcp.approx.ftz(scale) and -rcp * 2^23 of two neighbouring columns
+  uint32_t off2;        // their offsets as stored (half2)
+};
+__device__ __forceinline__ bool dq_pair_ok(DqPairHalf const &c) { // both reciprocals finite
+  return ((__float_as_uint(c.r0) & 0x7F800000u) != 0x7F800000u) && ((__float_as_uint(c.r1) & 0x7F800000u) != 0x7F800000u);
+}
+__device__ __forceinline__ DqPairHalf dq_pair_coef(__half s0, __half s1, uint32_t off2) {
+  DqPairHalf c;
+  c.r0 = rcp_approx_ftz(__half2float(s0));
+  c.r1 = rcp_approx_ftz(__half2float(s1));
+  c.c0 = -c.r0 * 8388608.f;
+  c.c1 = -c.r1 * 8388608.f;
+  c.off2 = off2;
+  return c;
+}
+// m0, m1 = 0x4B000000 | q of the two elements; returns the two dequantised halfs packed (element 0 in the low half)
+__device__ __forceinline__ uint32_t dq_pair(uint32_t m0, uint32_t m1, DqPairHalf const &c) {
+  float const f0 = __fmaf_rn(c.r0, __uint_as_float(m0), c.c0);
+  float const f1 = __fmaf_rn(c.r1, __uint_as_float(m1), c.c1);
+  __half2 const v = __floats2half2_rn(f0, f1);
+  __half2 const r = __hadd2(v, *reinterpret_cast<__half2 const *>(&c.off2));
+  return *reinterpret_cast<uint32_t const *>(&r);
+}
+constexpr uint32_t kDqMagic = 0x4B000000u;
+
 // bf16 variant (extension — the reference has no bf16): same recipe with bf16 roundings.
 struct DqCoefBf16 {
   float rcp;

@@ -11,6 +11,8 @@
 // fixed order through shared memory (deterministic).
 #include <cstdlib>
 
+#include <type_traits>
+
 #include "dequant.cuh"
 
 namespace ffb {
@@ -121,6 +123,55 @@ linear_stream_kernel(T const *__restrict__ A, uint8_t const *__restrict__ W, T c
             for (int nt = 0; nt < NT; nt++) {
               b0[nt] = word(w[u][nt], 2 * s);
               b1[nt] = word(w[u][nt], 2 * s + 1);
+            }
+          } else if (std::is_same<T, __half>::value && QB != 0) {
+            // two-at-a-time bit-exact rule (dequant.cuh): PRMT / LOP3 builds 2^23 + q, one FFMA per element, one
+            // packed convert and one HADD2 per pair
+            __half const *ps = reinterpret_cast<__half const *>(&sc[u][QB == 0 ? 0 : p]);
+            uint32_t const *ow = reinterpret_cast<uint32_t const *>(&of[u][QB == 0 ? 0 : p]);
+            int const e0 = (4 * s) % 8;
+            DqPairHalf const c01 = dq_pair_coef(ps[e0], ps[e0 + 1], ow[e0 / 2]);
+            DqPairHalf const c23 = dq_pair_coef(ps[e0 + 2], ps[e0 + 3], ow[e0 / 2 + 1]);
+            if (__all_sync(0xffffffffu, dq_pair_ok(c01) && dq_pair_ok(c23))) {
+#pragma unroll
+              for (int nt = 0; nt < NT; nt++) {
+                uint32_t m0, m1, m2, m3;
+                if (QB == 8) {
+                  uint32_t const v = word(w[u][nt], s);
+                  m0 = __byte_perm(v, kDqMagic, 0x7540);
+                  m1 = __byte_perm(v, kDqMagic, 0x7541);
+                  m2 = __byte_perm(v, kDqMagic, 0x7542);
+                  m3 = __byte_perm(v, kDqMagic, 0x7543);
+                } else { // even element = high nibble of its byte (decompress_kernels.cu:43-50)
+                  uint32_t const v = word(w[u][nt], s / 2) >> (16 * (s & 1));
+                  m0 = ((v >> 4) & 0xFu) | kDqMagic;
+                  m1 = (v & 0xFu) | kDqMagic;
+                  m2 = ((v >> 12) & 0xFu) | kDqMagic;
+                  m3 = ((v >> 8) & 0xFu) | kDqMagic;
+                }
+                b0[nt] = dq_pair(m0, m1, c01);
+                b1[nt] = dq_pair(m2, m3, c23);
+              }
+            } else { // a scale of 0 / NaN somewhere in the warp's columns: element-wise rule
+              DqCoefHalf cf[4];
+              __half const *po = reinterpret_cast<__half const *>(&of[u][QB == 0 ? 0 : p]);
+#pragma unroll
+              for (int e = 0; e < 4; e++) {
+                cf[e] = dq_coef(ps[e0 + e], po[e0 + e]);
+              }
+#pragma unroll
+              for (int nt = 0; nt < NT; nt++) {
+                int q0, q1, q2, q3;
+                if (QB == 8) {
+                  uint32_t const v = word(w[u][nt], s);
+                  q0 = v & 0xFF; q1 = (v >> 8) & 0xFF; q2 = (v >> 16) & 0xFF; q3 = v >> 24;
+                } else {
+                  uint32_t const v = (word(w[u][nt], s / 2) >> (16 * (s & 1))) & 0xFFFFu;
+                  q0 = (v >> 4) & 0xF; q1 = v & 0xF; q2 = (v >> 12) & 0xF; q3 = (v >> 8) & 0xF;
+                }
+                b0[nt] = pack2<__half>(dq_elem(q0, cf[0]), dq_elem(q1, cf[1]));
+                b1[nt] = pack2<__half>(dq_elem(q2, cf[2]), dq_elem(q3, cf[3]));
+              }
             }
           } else {
             typename DqCoef<T>::type cf[4];

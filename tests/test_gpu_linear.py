@@ -39,12 +39,13 @@ def test_dequant_bit_exact(bits, shape):
 
 
 def test_dequant_exhaustive_quotients():
-    """Every (q in 0..255) x (positive normal half scale) pair: the GPU's rcp.approx-based __hdiv recipe
-    against the oracle's IEEE division (host branch of __hdiv).  Pins the oracle for ALL inputs."""
-    # scales: all positive finite halfs >= 2^-14 ... each group column holds one scale; 32 rows hold q values.
-    scales = np.arange(0x0400, 0x7C00, dtype=np.uint16)  # 30720 positive normal halfs
+    """Every (q in 0..255) x (finite non-zero half scale: both signs, subnormals included) pair: the GPU's
+    rcp.approx-based __hdiv recipe (two-at-a-time form, csrc/dequant.cuh) against the oracle's IEEE division (host
+    branch of __hdiv).  Pins the oracle - and the dead correction branch - for ALL inputs."""
+    pos = np.arange(0x0001, 0x7C00, dtype=np.uint16)
+    scales = np.concatenate([pos, pos | 0x8000, pos[:2]])  # 63488 = multiple of 8; one column per scale
     n = len(scales)
-    in_dim = n  # one column per scale
+    in_dim = n
     mism = 0
     for qbase in range(0, 256, 32):
         out_dim = 32
@@ -58,6 +59,46 @@ def test_dequant_exhaustive_quotients():
         got = _gpu_dequant(blob, 8, in_dim, out_dim)
         mism += int((got != want).sum())
     assert mism == 0, mism
+
+
+def test_dequant_degenerate_scales_take_the_elementwise_rule():
+    """scale = 0 / inf / NaN columns (never produced by the quantiser): the pair rule needs a finite reciprocal, so
+    these fall back to the element-wise __hdiv recipe; finite results must still match, the rest must be non-finite."""
+    in_dim, out_dim = 64, 32
+    blob = np.zeros(O.blob_bytes(8, in_dim, out_dim), dtype=np.uint8)
+    blob[: in_dim * out_dim] = np.arange(in_dim * out_dim, dtype=np.uint32).astype(np.uint8)
+    meta = blob[in_dim * out_dim:].view(np.uint16)
+    meta[:in_dim] = 0x3555
+    meta[in_dim:] = 0x4D00  # 20.0
+    meta[in_dim + 3], meta[in_dim + 10], meta[in_dim + 17] = 0x0000, 0x7C00, 0x7E00
+    want = O.dequant(blob, 8, in_dim, out_dim).view(np.float16).astype(np.float32)
+    got = _gpu_dequant(blob, 8, in_dim, out_dim).view(np.float16).astype(np.float32)
+    fin = np.isfinite(want)
+    assert (got[fin] == want[fin]).all() and not np.isfinite(got[~fin]).any()
+
+
+@pytest.mark.parametrize("quant", [8, 4])
+def test_linear_stream_dequantises_bit_exactly(quant, monkeypatch):
+    """The weight-streaming GEMM dequantises in registers (byte / nibble extraction of its own): with one-hot
+    activations row m of the output IS column k0+m of the dequantised matrix, so it can be compared bit for bit."""
+    torch = _torch()
+    from flexflow_b200 import ops
+    monkeypatch.setenv("FFB_LINEAR", "stream")
+    K, N = 256, 96
+    rng = np.random.default_rng(5)
+    w = (rng.standard_normal((N, K)) * 0.05).astype(np.float32)
+    blob = O.quantize(w, quant)
+    want = O.dequant(blob, quant, K, N)  # [N][K] half bits
+    h = ops.FFHandler("cuda:0")
+    m = ops.LinearMeta(h, K, N, quantization_type=B.DT_INT8 if quant == 8 else B.DT_INT4, max_tokens_per_batch=16)
+    bdev = torch.from_numpy(blob).cuda()
+    for k0 in range(0, K, 16):
+        x = torch.zeros(16, K, dtype=torch.float16, device="cuda")
+        x[torch.arange(16), k0 + torch.arange(16)] = 1.0
+        out = torch.empty(16, N, dtype=torch.float16, device="cuda")
+        ops.Linear.inference_kernel_wrapper(m, None, x, out, bdev, None, K, N, 16)
+        got = out.cpu().numpy().view(np.uint16)
+        assert (got == want.view(np.uint16)[:, k0:k0 + 16].T).all(), k0
 
 
 @pytest.mark.parametrize("dtype", ["half", "bf16"])
