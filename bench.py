@@ -90,6 +90,27 @@ def attn_algorithmic_bytes(n_q_local, n_kv_local):
     return kv + qkv_in + out + append
 
 
+def ncu_traffic_bytes(csv_name):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
+    `ncu --set full` capture of this workload (profiles/, same shapes: the traffic does not depend on the run);
+    None when the capture is not there."""
+    import csv
+    path = os.path.join(ROOT, "profiles", csv_name)
+    if not os.path.exists(path):
+        return None
+    try:
+        rows = list(csv.reader(open(path)))
+        head, units, first = rows[0], rows[1], rows[2]
+        mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        tot = 0.0
+        for name in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            i = head.index(name)
+            tot += float(first[i].replace(",", "")) * mult[units[i]]
+        return tot
+    except Exception:  # noqa: BLE001
+        return None
+
+
 def attn_kernel_ms(step_fn, attn_metas, reps):
     """Average duration of the dominant attention kernel: CUDA events recorded around it inside the C ABI
     (ffb_attn_set_profiling; on the stream the kernel is launched on), eager launches.  The GPU is kept ~1 ms behind
@@ -258,7 +279,7 @@ def run_ours(args):
         "gpu_launches": args.steps * LAYERS * 5,
         "clocks": clocks,
         "roofline": {"kernel": "decode_attn_kernel<half,128,8>", "bound": "hbm", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_kind, "traffic": None,
+                     "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_kind, "traffic": ncu_traffic_bytes("r01_decode_attn_ncu_full_raw.csv") if tp == 1 else None,
                      "kernel_ms": k_ms, "kernel_timing": k_how, "algorithmic_bytes_per_launch": alg,
                      "attn_share_of_step": k_ms * LAYERS / ms_dev},
     }
@@ -480,6 +501,13 @@ def tree_verify_extra(args, dev, comm, rank, tp, decode_model, g):
         ms = sorted(lin[kind])[len(lin[kind]) // 2]
         tf = 2.0 * T * K_ * N_ / (ms * 1e-3) / 1e12
         res[kind] = {"M": T, "K": K_, "N": N_, "ms": ms, "tflops": tf, "frac_of_measured_bf16_peak": tf / tf_peak}
+    if tp == 1 and graph is not None:
+        # what is left of the graph-replayed step after the graph-timed GEMMs: prep (RoPE + KV append) + attention
+        # per layer as they run inside the step (no event, no launch latency): an upper bound of the attention kernel
+        rest = ms_step / LAYERS - res["qkv_proj"]["ms"] - res["o_proj"]["ms"]
+        res["prep_plus_attn_ms_in_graph_step"] = rest
+        res["attn_frac_of_hbm_peak_lower_bound_in_graph_step"] = alg / (rest * 1e-3) / 1e9 / peak
+        res["attn_dram_traffic_bytes_ncu"] = ncu_traffic_bytes("r01_attn_tc_ncu_full_raw.csv")
     for m in attn_metas:
         m.close()
     return res
