@@ -59,7 +59,7 @@ __device__ __forceinline__ __half dq_elem(int q, DqCoefHalf const &c) {
 //     |rcp| < 8.5e-6, i.e. |scale| > 117000: no half is that large (max 65504; scale = inf gives rcp = 0 and the
 //     quotient 0, also outside the range), so the branch is dead for every possible blob.
 //     tests/test_gpu_linear.py::test_dequant_exhaustive_quotients checks every q x every finite non-zero half scale
-//     through this path against the oracle's IEEE division.
+//     through this path against the CPU checker's IEEE division.
 struct DqPairHalf {
   float r0, c0, r1, c1; // rcp.approx.ftz(scale) and -rcp * 2^23 of two neighbouring columns
   uint32_t off2;        // their offsets as stored (half2)
