@@ -24,6 +24,7 @@ SOURCES = [
     "linear_tc2.cu",
     "capi_linear.cu",
     "comm.cu",
+    "norm_argmax.cu",
     "host_tree.cu",
 ]
 NVCC_FLAGS = [

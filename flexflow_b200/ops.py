@@ -287,3 +287,51 @@ def decompress_weights(blob, in_dim, out_dim, quant_type, dtype=torch.float16):
     L.check(fn(_ptr(blob), _ptr(out), in_dim, out_dim, B.DT_HALF if dtype == torch.float16 else B.DT_BF16, _stream()),
             "ffb_dequant")
     return out
+
+
+class ResidualRMSNormMeta:
+    """ResidualRMSNormMeta / RMSNormMeta (include/flexflow/ops/residual_rms_norm.h, rms_norm.h): eps and in_dim; the
+    reference's rms_ptr / norm_ptr scratch does not exist here (the row stays in registers)."""
+
+    def __init__(self, handler, eps, in_dim):
+        self.handle, self.eps, self.in_dim = handler, float(eps), int(in_dim)
+
+
+class ResidualRMSNorm:
+    @staticmethod
+    def inference_kernel_wrapper(m, bc, input1, input2, weight, residual_output, output):
+        """Kernels::ResidualRMSNorm::inference_kernel_wrapper (src/ops/kernels/residual_rms_norm_kernels.cu:205-232)."""
+        n = input1.numel() // m.in_dim
+        L.check(L.load().ffb_residual_rms_norm(_ptr(input1), _ptr(input2), _ptr(weight), _ptr(residual_output),
+                                               _ptr(output), n, m.in_dim, m.eps, _dt_of(input1), _stream()),
+                "ffb_residual_rms_norm")
+
+
+class RMSNorm:
+    @staticmethod
+    def inference_kernel_wrapper(m, bc, input, weight, output):
+        """Kernels::RMSNorm::inference_kernel_wrapper (src/ops/kernels/rms_norm_kernels.cu:148-190)."""
+        n = input.numel() // m.in_dim
+        L.check(L.load().ffb_residual_rms_norm(_ptr(input), C.c_void_p(0), _ptr(weight), C.c_void_p(0), _ptr(output),
+                                               n, m.in_dim, m.eps, _dt_of(input), _stream()), "ffb_residual_rms_norm")
+
+
+class ArgMaxMeta:
+    """ArgMaxMeta (include/flexflow/ops/argmax.h): beam_search selects the prob / parent outputs."""
+
+    def __init__(self, handler, beam_search=False):
+        self.handle, self.beam_search = handler, bool(beam_search)
+
+
+class ArgMax:
+    @staticmethod
+    def forward_kernel_wrapper(m, bc, input, indices, parent, batch_size):
+        """ArgMax::forward_kernel_wrapper (src/ops/argmax.cu:156-206): input [batch_size][length] DT, indices int32
+        [batch_size]; returns the probs tensor in the beam-search case (the reference keeps it in m->probs)."""
+        length = input.numel() // batch_size
+        if indices.dtype != torch.int32:
+            raise L.FFBError("indices must be int32")
+        probs = torch.empty(batch_size, dtype=torch.float32, device=input.device) if m.beam_search else None
+        L.check(L.load().ffb_argmax(_ptr(input), _ptr(indices), _ptr(probs), _ptr(parent) if m.beam_search else
+                                    C.c_void_p(0), batch_size, length, _dt_of(input), _stream()), "ffb_argmax")
+        return probs

@@ -183,6 +183,25 @@ int ffb_comm_has_peer(ffb_comm_t c);
 int ffb_linear_forward_allreduce(ffb_linear_t h, ffb_comm_t comm, void const *in_dev, void *out_dev,
                                  void const *weight_dev, void const *bias_dev, int batch, ffb_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------
+ * The two row operators either side of the chain that the reference's FusedOp spans.
+ *
+ * ffb_residual_rms_norm: Kernels::ResidualRMSNorm::inference_kernel_wrapper
+ * (src/ops/kernels/residual_rms_norm_kernels.cu:97-164,205-232): residual_output = input1 + input2 (in DT),
+ * rms = DT(rsqrt(mean(residual_output^2) + eps)), output = DT(DT(residual_output * rms) * weight).
+ * input2_dev == NULL gives Kernels::RMSNorm::inference_kernel_wrapper (src/ops/kernels/rms_norm_kernels.cu:97-146)
+ * on input1 (residual_output_dev is then not written).  Roundings and the fp32 summation order are the
+ * reference's.  All tensors [num_tokens][dim] DT, weight [dim] DT; dim % 32 == 0, dim <= 16384.
+ *
+ * ffb_argmax: ArgMax::forward_kernel (src/ops/argmax.cu:64-102): indices[t] = first index of the maximum of
+ * input[t][0..length); prob_dev (beam search: the maximum as float) and parent_dev (zeroed) may be NULL.
+ * ------------------------------------------------------------------------------------------ */
+int ffb_residual_rms_norm(void const *input1_dev, void const *input2_dev, void const *weight_dev,
+                          void *residual_output_dev, void *output_dev, int num_tokens, int dim, float eps, int dtype,
+                          ffb_stream_t stream);
+int ffb_argmax(void const *input_dev, int *indices_dev, float *prob_dev, int *parent_dev, int num_tokens, int length,
+               int dtype, ffb_stream_t stream);
+
 /* ---- host-side SpecInfer tree logic (integer only; runs on the host, no CUDA call) ---------------------------------
  * The bit masks these build are what ffb_tree_attn_forward / ffb_spec_attn_forward read from causalMask[], and
  * ffb_traverse_verify_tree turns the LLM's per-node outputs into the accepted tokens and the commit list of the next

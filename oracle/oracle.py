@@ -49,6 +49,8 @@ def lib():
         _lib.orc_update_bitmask.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
         _lib.orc_append_pending_request.argtypes = [C.c_void_p, C.c_int]
         _lib.orc_append_bitmask.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int]
+        _lib.orc_residual_rms_norm.argtypes = [C.c_void_p] * 5 + [C.c_int, C.c_int, C.c_float, C.c_int]
+        _lib.orc_argmax.argtypes = [C.c_void_p] * 4 + [C.c_int, C.c_int]
         _lib.orc_traverse_verify_tree.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 9
     return _lib
 
@@ -145,6 +147,53 @@ def linear(x, w, bias=None, dt="half"):
     lib().orc_linear_forward(_p(x), _p(w), _p(b) if b is not None else None, _p(out), x.shape[0], x.shape[1],
                              w.shape[0], DT_CODE[dt])
     return out
+
+
+def to_bits(x, dt="half"):
+    """float array -> uint16 bit patterns of DT (round to nearest even)."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    if dt == "half":
+        out = np.zeros(x.shape, dtype=np.uint16)
+        lib().orc_float_to_half_bits(_p(x), _p(out), x.size)
+        return out
+    r = round_to_dt(x, "bf16")
+    return (r.view(np.uint32) >> 16).astype(np.uint16)
+
+
+def from_bits(b, dt="half"):
+    b = np.ascontiguousarray(b, dtype=np.uint16)
+    if dt == "half":
+        out = np.zeros(b.shape, dtype=np.float32)
+        lib().orc_half_bits_to_float(_p(b), _p(out), b.size)
+        return out
+    return (b.astype(np.uint32) << 16).view(np.float32)
+
+
+def residual_rms_norm(x1_bits, x2_bits, weight_bits, eps, dt="half"):
+    """16-bit patterns in and out.  Returns (residual_output_bits or None, output_bits); x2_bits None = RMSNorm."""
+    x1 = np.ascontiguousarray(x1_bits, dtype=np.uint16)
+    rows, n = x1.shape
+    w = np.ascontiguousarray(weight_bits, dtype=np.uint16)
+    out = np.zeros_like(x1)
+    if x2_bits is None:
+        lib().orc_residual_rms_norm(_p(x1), None, _p(w), None, _p(out), rows, n, eps, DT_CODE[dt])
+        return None, out
+    x2 = np.ascontiguousarray(x2_bits, dtype=np.uint16)
+    res = np.zeros_like(x1)
+    lib().orc_residual_rms_norm(_p(x1), _p(x2), _p(w), _p(res), _p(out), rows, n, eps, DT_CODE[dt])
+    return res, out
+
+
+def argmax(x, beam_search=False):
+    """x: [rows][length] float32 (values already in DT).  Returns (indices, prob or None, parent or None)."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    rows, length = x.shape
+    idx = np.zeros(rows, dtype=np.int32)
+    prob = np.zeros(rows, dtype=np.float32) if beam_search else None
+    parent = np.full(rows, -1, dtype=np.int32) if beam_search else None
+    lib().orc_argmax(_p(x), _p(idx), _p(prob) if beam_search else None, _p(parent) if beam_search else None, rows,
+                     length)
+    return idx, prob, parent
 
 
 def traverse_verify_tree(in_tree, out_tree, committed):

@@ -1,0 +1,117 @@
+"""GPU parity of ffb_residual_rms_norm / ffb_argmax (csrc/norm_argmax.cu) against the oracle, through the C ABI."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def _dev_bits(a):
+    torch = _torch()
+    return torch.from_numpy(np.ascontiguousarray(a).view(np.int16)).cuda()
+
+
+def _gpu_norm(x1, x2, w, eps, dt):
+    torch = _torch()
+    from flexflow_b200 import batch_config as B
+    from flexflow_b200 import lib as L
+    code = B.DT_HALF if dt == "half" else B.DT_BF16
+    d1, dw = _dev_bits(x1), _dev_bits(w)
+    d2 = _dev_bits(x2) if x2 is not None else None
+    res = torch.zeros_like(d1) if x2 is not None else None
+    out = torch.zeros_like(d1)
+    p = lambda t: C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+    rows, n = x1.shape
+    L.check(L.load().ffb_residual_rms_norm(p(d1), p(d2), p(dw), p(res), p(out), rows, n, eps, code,
+                                           C.c_void_p(torch.cuda.current_stream().cuda_stream)), "rms_norm")
+    torch.cuda.synchronize()
+    return (None if res is None else res.cpu().numpy().view(np.uint16)), out.cpu().numpy().view(np.uint16)
+
+
+@pytest.mark.parametrize("dt", ["half", "bf16"])
+@pytest.mark.parametrize("n", [64, 768, 4096, 5120, 8192, 16384])
+@pytest.mark.parametrize("residual", [False, True])
+def test_rms_norm_bit_exact(dt, n, residual):
+    """Same roundings and the same fp32 summation order as the reference kernel, so every row is the oracle's bit for
+    bit unless rsqrtf's 2 ulp move the 16-bit rms across a rounding boundary (rare: counted, and bounded)."""
+    rng = np.random.default_rng(n * 2 + residual)
+    rows = 67
+    x1 = O.to_bits(rng.standard_normal((rows, n)).astype(np.float32) * 1.5, dt)
+    x2 = O.to_bits(rng.standard_normal((rows, n)).astype(np.float32), dt) if residual else None
+    w = O.to_bits(1.0 + 0.1 * rng.standard_normal(n).astype(np.float32), dt)
+    want_res, want = O.residual_rms_norm(x1, x2, w, 1e-5, dt)
+    res, got = _gpu_norm(x1, x2, w, 1e-5, dt)
+    if residual:
+        assert np.array_equal(res, want_res)
+    same = (got == want).all(axis=1)
+    assert same.mean() >= 0.97, same.mean()
+    np.testing.assert_allclose(O.from_bits(got, dt), O.from_bits(want, dt), rtol=1e-2, atol=1e-6)
+
+
+def test_rms_norm_large_batch_and_errors():
+    torch = _torch()
+    from flexflow_b200 import lib as L
+    rng = np.random.default_rng(5)
+    x1 = O.to_bits(rng.standard_normal((1024, 4096)).astype(np.float32), "half")
+    x2 = O.to_bits(rng.standard_normal((1024, 4096)).astype(np.float32), "half")
+    w = O.to_bits(np.ones(4096, dtype=np.float32), "half")
+    want_res, want = O.residual_rms_norm(x1, x2, w, 1e-6, "half")
+    res, got = _gpu_norm(x1, x2, w, 1e-6, "half")
+    assert np.array_equal(res, want_res)
+    assert (got == want).all(axis=1).mean() >= 0.99
+    with pytest.raises(L.FFBError):
+        _gpu_norm(x1[:, :40], None, w[:40], 1e-6, "half")  # dim % 32 != 0
+
+
+@pytest.mark.parametrize("dt", ["half", "bf16"])
+@pytest.mark.parametrize("shape", [(16, 32000), (512, 32000), (5, 1001), (3, 50257), (1, 128256)])
+def test_argmax_bit_exact(dt, shape):
+    torch = _torch()
+    from flexflow_b200 import ops
+    rng = np.random.default_rng(shape[0])
+    x = O.from_bits(O.to_bits(rng.standard_normal(shape).astype(np.float32), dt), dt)
+    x[0, 7] = x[0, shape[1] - 1] = 50.0  # tie across threads: smaller index wins
+    if shape[0] > 2:
+        x[1, :] = 1.0                     # all equal -> 0
+        x[2, -1] = 60.0                   # maximum in the scalar tail / last vector
+    want_idx, want_prob, _ = O.argmax(x, beam_search=True)
+    tdt = torch.float16 if dt == "half" else torch.bfloat16
+    d = torch.from_numpy(x).cuda().to(tdt)
+    idx = torch.full((shape[0],), -1, dtype=torch.int32, device="cuda")
+    parent = torch.full((shape[0],), -1, dtype=torch.int32, device="cuda")
+    probs = ops.ArgMax.forward_kernel_wrapper(ops.ArgMaxMeta(None, beam_search=True), None, d, idx, parent, shape[0])
+    torch.cuda.synchronize()
+    assert np.array_equal(idx.cpu().numpy(), want_idx)
+    assert np.array_equal(probs.cpu().numpy(), want_prob)
+    assert not parent.cpu().numpy().any()
+    idx2 = torch.full((shape[0],), -1, dtype=torch.int32, device="cuda")
+    assert ops.ArgMax.forward_kernel_wrapper(ops.ArgMaxMeta(None), None, d, idx2, None, shape[0]) is None
+    assert np.array_equal(idx2.cpu().numpy(), want_idx)
+
+
+def test_norm_wrappers_mirror_reference_names():
+    torch = _torch()
+    from flexflow_b200 import ops
+    rng = np.random.default_rng(9)
+    a = torch.from_numpy(rng.standard_normal((16, 4096)).astype(np.float16)).cuda()
+    b = torch.from_numpy(rng.standard_normal((16, 4096)).astype(np.float16)).cuda()
+    w = torch.from_numpy((1 + 0.1 * rng.standard_normal(4096)).astype(np.float16)).cuda()
+    res, out, out2 = torch.empty_like(a), torch.empty_like(a), torch.empty_like(a)
+    m = ops.ResidualRMSNormMeta(None, 1e-5, 4096)
+    ops.ResidualRMSNorm.inference_kernel_wrapper(m, None, a, b, w, res, out)
+    ops.RMSNorm.inference_kernel_wrapper(m, None, res, w, out2)
+    torch.cuda.synchronize()
+    assert torch.equal(res, a + b)
+    assert torch.equal(out, out2)  # norm(residual sum) == residual norm
+    want_res, want = O.residual_rms_norm(a.cpu().numpy().view(np.uint16), b.cpu().numpy().view(np.uint16),
+                                         w.cpu().numpy().view(np.uint16), 1e-5, "half")
+    assert (out.cpu().numpy().view(np.uint16) == want).all(axis=1).mean() >= 0.9
