@@ -288,6 +288,11 @@ def run_ours(args):
             line["quantized_decode"] = quantized_extra(args, dev, model, step, ms_dev)
         except Exception as e:  # the headline line must still print
             line["quantized_decode"] = {"error": repr(e)}
+    if tp == 1:
+        try:
+            line["block_ops"] = block_ops_extra(dev)
+        except Exception as e:  # the headline line must still print
+            line["block_ops"] = {"error": repr(e)}
     if not args.no_tree_verify:
         try:
             line["tree_verify"] = tree_verify_extra(args, dev, comm, rank, tp, model, g)
@@ -381,6 +386,57 @@ def quantized_extra(args, dev, model, step, ms_fp16):
     finally:
         for l, (m, w) in zip(lins, saved):
             l.meta, l.weight = m, w
+    return res
+
+
+def block_ops_extra(dev):
+    """ResidualRMSNorm (input of qkv_proj) and ArgMax (token ids for accept / reject) at the decode
+    and tree-verify batch sizes; graph replay of 40 launches over rotating buffers, algorithmic bytes over the
+    measured HBM peak (both are latency-bound at 16 rows)."""
+    import torch
+    from flexflow_b200 import ops
+    peak, _ = peaks()
+    res = {}
+
+    def timed(fn, nbuf, reps=40):
+        for i in range(3):
+            fn(i % nbuf)
+        torch.cuda.synchronize()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            for i in range(reps):
+                fn(i % nbuf)
+        gr.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(5):
+            gr.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / (5 * reps)
+
+    for rows in (BATCH, 512):
+        nbuf = 8
+        a = [torch.randn(rows, HIDDEN, device=dev).half() for _ in range(nbuf)]
+        b = [torch.randn(rows, HIDDEN, device=dev).half() for _ in range(nbuf)]
+        w = torch.ones(HIDDEN, device=dev).half()
+        r, o = torch.empty_like(a[0]), torch.empty_like(a[0])
+        m = ops.ResidualRMSNormMeta(None, 1e-5, HIDDEN)
+        ms = timed(lambda i: ops.ResidualRMSNorm.inference_kernel_wrapper(m, None, a[i], b[i], w, r, o), nbuf)
+        alg = rows * HIDDEN * 2 * 4 + HIDDEN * 2
+        res["residual_rms_norm_%dx%d" % (rows, HIDDEN)] = {"us": ms * 1e3, "algorithmic_bytes": alg,
+                                                            "gbs": alg / (ms * 1e-3) / 1e9,
+                                                            "frac_of_hbm_peak": alg / (ms * 1e-3) / 1e9 / peak}
+        vocab = 32000
+        x = [torch.randn(rows, vocab, device=dev).half() for _ in range(nbuf)]
+        idx = torch.empty(rows, dtype=torch.int32, device=dev)
+        am = ops.ArgMaxMeta(None)
+        ms = timed(lambda i: ops.ArgMax.forward_kernel_wrapper(am, None, x[i], idx, None, rows), nbuf)
+        alg = rows * vocab * 2 + rows * 4
+        res["argmax_%dx%d" % (rows, vocab)] = {"us": ms * 1e3, "algorithmic_bytes": alg,
+                                               "gbs": alg / (ms * 1e-3) / 1e9,
+                                               "frac_of_hbm_peak": alg / (ms * 1e-3) / 1e9 / peak}
     return res
 
 

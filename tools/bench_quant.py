@@ -1,0 +1,56 @@
+"""Quantised decode projections (BASELINE configs[2]): us per launch and GB/s of blob bytes at M = 16.
+    python tools/bench_quant.py [--only int8|int4] [--layer qkv_proj|o_proj] [--json out.json]"""
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from flexflow_b200 import batch_config as B  # noqa: E402
+from flexflow_b200 import ops  # noqa: E402
+from tools.bench_linear import time_ms  # noqa: E402
+
+
+def make_blob(K, N, bits, gen):
+    nvals = K * N * bits // 8
+    meta = torch.empty(K * N // 32, dtype=torch.float16, device="cuda")
+    return torch.cat([torch.randint(0, 256, (nvals,), generator=gen, device="cuda", dtype=torch.uint8),
+                      meta.fill_(-0.04).clone().view(torch.uint8),
+                      meta.fill_((2 ** bits - 1) / 0.08).clone().view(torch.uint8)])
+
+
+def main():
+    h = ops.FFHandler("cuda:0")
+    only = sys.argv[sys.argv.index("--only") + 1] if "--only" in sys.argv else None
+    only_layer = sys.argv[sys.argv.index("--layer") + 1] if "--layer" in sys.argv else None
+    M = int(sys.argv[sys.argv.index("--m") + 1]) if "--m" in sys.argv else 16
+    gen = torch.Generator(device="cuda").manual_seed(7)
+    res = []
+    for lname, K, N in (("qkv_proj", 4096, 12288), ("o_proj", 4096, 4096)):
+        if only_layer and lname != only_layer:
+            continue
+        for name, qt, bits in (("int8", B.DT_INT8, 8), ("int4", B.DT_INT4, 4)):
+            if only and name != only:
+                continue
+            nb = 6 if lname == "qkv_proj" else 16  # rotate blobs: > L2
+            blobs = [make_blob(K, N, bits, gen) for _ in range(nb)]
+            m = ops.LinearMeta(h, K, N, torch.float16, qt, 64)
+            x = torch.randn(M, K, device="cuda").half()
+            out = torch.empty(M, N, device="cuda", dtype=torch.float16)
+            i = [0]
+
+            def fn():
+                i[0] += 1
+                ops.Linear.forward_kernel_wrapper(m, x, out, blobs[i[0] % nb], None, K, N, M)
+            ms = time_ms(fn, iters=24)
+            res.append(dict(layer=lname, quant=name, M=M, us=ms * 1e3, blob_mb=blobs[0].numel() / 1e6,
+                            blob_gbs=blobs[0].numel() / ms / 1e6))
+            print(res[-1], flush=True)
+            del blobs
+    if "--json" in sys.argv:
+        json.dump(res, open(sys.argv[sys.argv.index("--json") + 1], "w"), indent=1)
+
+
+if __name__ == "__main__":
+    main()
