@@ -20,6 +20,7 @@ SOURCES = [
     "dequant.cu",
     "linear_stream.cu",
     "linear_gemv.cu",
+    "linear_qgemv.cu",
     "linear_tc.cu",
     "linear_tc2.cu",
     "capi_linear.cu",

@@ -16,6 +16,9 @@ int linear_gemv_supported(int quant, int M, int K, int N);
 int launch_linear_gemv(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N,
                        cudaStream_t s);
 // fused o_proj + NVLink AllReduce for decode batches (linear_gemv.cu)
+int linear_qgemv_supported(int dtype, int quant, int M, int K, int N);
+int launch_linear_qgemv(int quant, void const *in, void *out, void const *w, void const *bias, int M, int K, int N,
+                        cudaStream_t s);
 int linear_gemv_allreduce_supported(PeerTable const *pt, int quant, int M, int K, int N);
 int launch_linear_gemv_allreduce(PeerTable const *pt, int dtype, void const *in, void *out, void const *w, void const *bias,
                                  int M, int K, int N, cudaStream_t s);
@@ -108,6 +111,16 @@ int ffb_linear_forward(ffb_linear_t h, void const *in, void *out, void const *w,
   bool const force_stream = force && strcmp(force, "stream") == 0;
   if (!force_stream && linear_gemv_supported(d.quant_type, batch, d.in_dim, d.out_dim)) {
     return launch_linear_gemv(d.dtype, in, out, w, bias, batch, d.in_dim, d.out_dim, s);
+  }
+  // quantised blobs, decode batches: the persistent bulk-copy kernel with per-(group, column) reciprocals in shared
+  // memory (linear_qgemv.cu) when the layer has at most one 32-feature group per SM (o_proj: 11.4 / 11.8 us for int8 /
+  // int4 against 11.5 / 12.4 us in the stream kernel); wider layers (qkv_proj, 384 groups = 3 tiles on the busiest
+  // CTA) are level with the stream kernel (24.3 / 26.9 against 23.2 / 26.4 us) and stay there.  FFB_LINEAR=qgemv /
+  // stream force either for A/B.
+  bool const force_qgemv = force && strcmp(force, "qgemv") == 0;
+  if (!force_stream && (force_qgemv || d.out_dim / 32 <= kNumSMs) &&
+      linear_qgemv_supported(d.dtype, d.quant_type, batch, d.in_dim, d.out_dim)) {
+    return launch_linear_qgemv(d.quant_type, in, out, w, bias, batch, d.in_dim, d.out_dim, s);
   }
   size_t const elt = 2;
   for (int m0 = 0; m0 < batch; m0 += 64) {

@@ -44,12 +44,16 @@ template <typename T> __device__ __forceinline__ uint32_t pack2(T a, T b) {
 }
 
 constexpr int LS_WARPS = 8;
+// Decode (MT == 1) occupancy, measured on the 7B qkv_proj blob (384 CTAs): int8 with one chunk in flight per warp and
+// 3 CTAs per SM (80 registers: every CTA resident in one wave) 23 us, against 35 us with two chunks and 2 CTAs per SM
+// (1.3 waves, ncu: long-scoreboard stalls); int4 needs its 128 registers (39 us at 3 CTAs per SM, 26 us at 2).
+template <int QB> struct LsOcc { static constexpr int BLOCKS = QB == 8 ? 3 : 2; };
 
 // QB: 0 = DT weights, 8 = int8 blob, 4 = int4 blob.  The k -> mma-slot assignment is a fixed
 // permutation applied identically to A and B (a dot product is order-free), chosen so every lane
 // reads 16 contiguous bytes of a weight row.
 template <typename T, int QB, int NT, int MT>
-__global__ void __launch_bounds__(LS_WARPS * 32, MT == 1 ? 2 : 1)
+__global__ void __launch_bounds__(LS_WARPS * 32, MT == 1 ? LsOcc<QB>::BLOCKS : 1)
 linear_stream_kernel(T const *__restrict__ A, uint8_t const *__restrict__ W, T const *__restrict__ bias,
                      T *__restrict__ out, int M, int K, int N) {
   constexpr int KE = QB == 0 ? 8 : (QB == 8 ? 16 : 32); // k elements per lane per chunk (16 B of weights)
@@ -79,7 +83,7 @@ linear_stream_kernel(T const *__restrict__ A, uint8_t const *__restrict__ W, T c
   // U chunks per warp are fetched back-to-back BEFORE any of them is consumed, so U*(NT + 2*MT*AP [+ 2*AP])
   // 16-byte loads are in flight per lane: at M <= 16 the kernel is a pure weight stream and its speed is
   // set by bytes in flight, not by the MMAs.
-  constexpr int U = MT == 1 ? (QB == 0 ? 4 : (QB == 8 ? 2 : 1)) : ((MT == 2 && QB == 0) ? 2 : 1);
+  constexpr int U = MT == 1 ? (QB == 0 ? 4 : 1) : ((MT == 2 && QB == 0) ? 2 : 1);
   constexpr int QP = QB == 0 ? 1 : AP;
   for (int kc0 = warp; kc0 < nchunks; kc0 += LS_WARPS * U) {
     uint4 w[U][NT], sc[U][QP], of[U][QP], alo[U][MT][AP], ahi[U][MT][AP];

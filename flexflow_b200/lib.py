@@ -8,7 +8,8 @@ import os
 from . import batch_config as bcfg
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libffb200.so")
+# FFB_LIB_PATH: load another build of the same sources (kernel A/B experiments, trace builds)
+LIB_PATH = os.environ.get("FFB_LIB_PATH") or os.path.join(_HERE, "libffb200.so")
 
 
 class FFBError(RuntimeError):

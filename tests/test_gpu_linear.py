@@ -187,3 +187,94 @@ def test_linear_bias_and_errors():
                                           None, K, N, 9)
     with pytest.raises(FFBError):
         ops.LinearMeta(h, 100, 64)
+
+
+# ---- persistent quantised decode kernel (csrc/linear_qgemv.cu): the default for int8 / int4 blobs at <= 16 tokens ----
+
+def _one_hot_columns(m, bdev, K, N, k0s):
+    torch = _torch()
+    from flexflow_b200 import ops
+    got = {}
+    for k0 in k0s:
+        x = torch.zeros(16, K, dtype=torch.float16, device="cuda")
+        x[torch.arange(16), k0 + torch.arange(16)] = 1.0
+        out = torch.empty(16, N, dtype=torch.float16, device="cuda")
+        ops.Linear.inference_kernel_wrapper(m, None, x, out, bdev, None, K, N, 16)
+        got[k0] = out.cpu().numpy().view(np.uint16)
+    return got
+
+
+@pytest.mark.parametrize("quant", [8, 4])
+@pytest.mark.parametrize("K,N", [(1024, 96), (2048, 160), (4096, 4768)])
+def test_linear_qgemv_dequantises_bit_exactly(quant, K, N, monkeypatch):
+    """One-hot activations: row m of the output IS column k0+m of the dequantised matrix (fp32 accumulation of one
+    non-zero term), so the kernel's on-chip dequantisation is compared bit for bit with the oracle's.  N = 4768 = 149
+    groups gives one CTA a second tile (ring wrap-around, coefficient double buffer across a tile boundary)."""
+    torch = _torch()
+    from flexflow_b200 import ops
+    monkeypatch.setenv("FFB_LINEAR", "qgemv")
+    rng = np.random.default_rng(K + quant)
+    w = (rng.standard_normal((N, K)) * 0.05).astype(np.float32)
+    blob = O.quantize(w, quant)
+    want = O.dequant(blob, quant, K, N).view(np.uint16)
+    m = ops.LinearMeta(ops.FFHandler("cuda:0"), K, N, quantization_type=B.DT_INT8 if quant == 8 else B.DT_INT4,
+                       max_tokens_per_batch=16)
+    k0s = list(range(0, K, 16)) if K <= 2048 else list(range(0, K, 16))[::5] + [K - 16]
+    got = _one_hot_columns(m, torch.from_numpy(blob).cuda(), K, N, k0s)
+    for k0 in k0s:
+        assert (got[k0] == want[:, k0:k0 + 16].T).all(), k0
+
+
+@pytest.mark.parametrize("quant", [8, 4])
+@pytest.mark.parametrize("M", [1, 7, 16])
+@pytest.mark.parametrize("K,N", [(2048, 4128), (4096, 12288)])
+def test_linear_qgemv_matches_oracle(quant, M, K, N, monkeypatch):
+    torch = _torch()
+    from flexflow_b200 import ops
+    monkeypatch.setenv("FFB_LINEAR", "qgemv")
+    rng = np.random.default_rng(M + K)
+    x = O.round_to_dt(rng.standard_normal((M, K)).astype(np.float32), "half")
+    w = (rng.standard_normal((N, K)) * 0.05).astype(np.float32)
+    bias = O.round_to_dt(rng.standard_normal(N).astype(np.float32), "half")
+    blob = O.quantize(w, quant)
+    wq = O.dequant(blob, quant, K, N).view(np.float16).astype(np.float32)
+    m = ops.LinearMeta(ops.FFHandler("cuda:0"), K, N, quantization_type=B.DT_INT8 if quant == 8 else B.DT_INT4,
+                       max_tokens_per_batch=16)
+    out = torch.empty(M, N, dtype=torch.float16, device="cuda")
+    ops.Linear.inference_kernel_wrapper(m, None, torch.from_numpy(x).cuda().half(), out, torch.from_numpy(blob).cuda(),
+                                        torch.from_numpy(bias).cuda().half(), K, N, M)
+    torch.cuda.synchronize()
+    want = O.linear(x, wq, bias, "half")
+    got = out.float().cpu().numpy()
+    assert np.abs(got - want).max() <= 2e-3 * max(1.0, np.abs(want).max())
+    # same call again: the fixed-order reduction makes the result reproducible bit for bit
+    out2 = torch.empty_like(out)
+    ops.Linear.inference_kernel_wrapper(m, None, torch.from_numpy(x).cuda().half(), out2, torch.from_numpy(blob).cuda(),
+                                        torch.from_numpy(bias).cuda().half(), K, N, M)
+    assert torch.equal(out, out2)
+
+
+@pytest.mark.parametrize("quant", [8, 4])
+def test_linear_qgemv_zero_scale_takes_the_elementwise_rule(quant, monkeypatch):
+    """A scale of 0 makes every weight of its column inf / NaN in the reference (q / 0 + offset); the stage that holds
+    it falls back to the element-wise rule, the other groups and the group's other stages stay on the pair rule."""
+    torch = _torch()
+    from flexflow_b200 import ops
+    monkeypatch.setenv("FFB_LINEAR", "qgemv")
+    K, N = 2048, 96
+    rng = np.random.default_rng(3)
+    w = (rng.standard_normal((N, K)) * 0.05).astype(np.float32)
+    blob = O.quantize(w, quant).copy()
+    nvals = K * N * quant // 8
+    scales = blob[nvals + 2 * (K * N // 32):].view(np.float16)
+    scales[1 * K + 5] = 0.0   # group 1, column 5 (stage 0)
+    want = O.dequant(blob, quant, K, N).view(np.uint16)
+    m = ops.LinearMeta(ops.FFHandler("cuda:0"), K, N, quantization_type=B.DT_INT8 if quant == 8 else B.DT_INT4,
+                       max_tokens_per_batch=16)
+    k0s = [0, 16, 1024, 2032]
+    got = _one_hot_columns(m, torch.from_numpy(blob).cuda(), K, N, k0s)
+    for k0 in k0s:
+        ok = np.r_[0:32, 64:96]
+        assert (got[k0][:, ok] == want[ok, k0:k0 + 16].T).all(), k0
+        g1 = got[k0][:, 32:64].view(np.float16)
+        assert not np.isfinite(g1).any()  # inf, or 0 * inf = NaN, in every dot product of the group
