@@ -94,6 +94,45 @@ template <int QB> struct QgCfg {
   static constexpr size_t SMEM = (size_t)STAGES * STAGE_BYTES + COEF_BYTES + RED_BYTES;
 };
 
+struct QgAcc {
+  float v[4][4];
+};
+// One stage with the element-wise rule (a scale of zero: rcp = inf, where the pair rule's fma(inf, m, -inf) would give
+// NaN for every q instead of inf for q >= 1).  Kept out of line so that its registers do not weigh on the fast path.
+template <int QB>
+__device__ __noinline__ QgAcc qg_slow_stage(QgAcc acc, uint4 w0, uint4 w1, uint4 w2, uint4 w3, uint4 al0, uint4 al1,
+                                            uint4 ah0, uint4 ah1, uint8_t const *scales_raw, uint8_t const *offs_raw,
+                                            int kl) {
+  uint4 const wv[4] = {w0, w1, w2, w3};
+#pragma unroll
+  for (int ks = 0; ks < 4; ks++) {
+    DqCoefHalf cf[4];
+#pragma unroll
+    for (int e = 0; e < 4; e++) {
+      int const col = kl + 4 * ks + e;
+      cf[e] = dq_coef(*reinterpret_cast<__half const *>(scales_raw + 2 * col),
+                      *reinterpret_cast<__half const *>(offs_raw + 2 * col));
+    }
+    uint4 const &al = ks < 2 ? al0 : al1, &ah = ks < 2 ? ah0 : ah1;
+    uint32_t const a0 = qg_word(al, (ks & 1) * 2), a2 = qg_word(al, (ks & 1) * 2 + 1);
+    uint32_t const a1 = qg_word(ah, (ks & 1) * 2), a3 = qg_word(ah, (ks & 1) * 2 + 1);
+#pragma unroll
+    for (int nt = 0; nt < 4; nt++) {
+      int q0, q1, q2, q3;
+      if (QB == 8) {
+        uint32_t const v = qg_word(wv[nt], ks);
+        q0 = v & 0xFF; q1 = (v >> 8) & 0xFF; q2 = (v >> 16) & 0xFF; q3 = v >> 24;
+      } else {
+        uint32_t const v = (qg_word(wv[nt], ks >> 1) >> (16 * (ks & 1))) & 0xFFFFu;
+        q0 = (v >> 4) & 0xF; q1 = v & 0xF; q2 = (v >> 12) & 0xF; q3 = (v >> 8) & 0xF;
+      }
+      qg_mma(acc.v[nt], a0, a1, a2, a3, qg_pack(dq_elem(q0, cf[0]), dq_elem(q1, cf[1])),
+             qg_pack(dq_elem(q2, cf[2]), dq_elem(q3, cf[3])));
+    }
+  }
+  return acc;
+}
+
 // SPT = K / 1024 stages per tile (1, 2 or 4)
 template <int QB, int SPT>
 __global__ void __launch_bounds__(QG_THREADS, 1)
@@ -249,31 +288,22 @@ linear_qgemv_kernel(__half const *__restrict__ A, uint8_t const *__restrict__ W,
             qg_mma(acc[nt], a0, a1, a2, a3, dq_pair(m0, m1, c01), dq_pair(m2, m3, c23));
           }
         }
-      } else { // a zero scale somewhere in this stage: element-wise rule with the raw scales
+      } else { // a zero scale somewhere in this stage: element-wise rule with the raw scales (out of line)
+        QgAcc r;
 #pragma unroll
-        for (int ks = 0; ks < 4; ks++) {
-          DqCoefHalf cf[4];
+        for (int nt = 0; nt < 4; nt++) {
 #pragma unroll
           for (int e = 0; e < 4; e++) {
-            int const col = kl + 4 * ks + e;
-            cf[e] = dq_coef(*reinterpret_cast<__half const *>(scales_raw + 2 * col),
-                            *reinterpret_cast<__half const *>(offs_raw + 2 * col));
+            r.v[nt][e] = acc[nt][e];
           }
-          uint4 const &al = alo[st][ks >> 1], &ah = ahi[st][ks >> 1];
-          uint32_t const a0 = qg_word(al, (ks & 1) * 2), a2 = qg_word(al, (ks & 1) * 2 + 1);
-          uint32_t const a1 = qg_word(ah, (ks & 1) * 2), a3 = qg_word(ah, (ks & 1) * 2 + 1);
+        }
+        r = qg_slow_stage<QB>(r, wv[0], wv[1], wv[2], wv[3], alo[st][0], alo[st][1], ahi[st][0], ahi[st][1], scales_raw,
+                              offs_raw, kl);
 #pragma unroll
-          for (int nt = 0; nt < 4; nt++) {
-            int q0, q1, q2, q3;
-            if (QB == 8) {
-              uint32_t const v = qg_word(wv[nt], ks);
-              q0 = v & 0xFF; q1 = (v >> 8) & 0xFF; q2 = (v >> 16) & 0xFF; q3 = v >> 24;
-            } else {
-              uint32_t const v = (qg_word(wv[nt], ks >> 1) >> (16 * (ks & 1))) & 0xFFFFu;
-              q0 = (v >> 4) & 0xF; q1 = v & 0xF; q2 = (v >> 12) & 0xF; q3 = (v >> 8) & 0xF;
-            }
-            qg_mma(acc[nt], a0, a1, a2, a3, qg_pack(dq_elem(q0, cf[0]), dq_elem(q1, cf[1])),
-                   qg_pack(dq_elem(q2, cf[2]), dq_elem(q3, cf[3])));
+        for (int nt = 0; nt < 4; nt++) {
+#pragma unroll
+          for (int e = 0; e < 4; e++) {
+            acc[nt][e] = r.v[nt][e];
           }
         }
       }

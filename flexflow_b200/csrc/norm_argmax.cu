@@ -128,14 +128,27 @@ argmax_kernel(T const *__restrict__ in, int *__restrict__ indices, float *__rest
   float best = -INFINITY;
   int bi = INT_MAX;
   int const nvec = ((size_t)row * V) % 8 == 0 ? V / 8 : 0; // 128-bit loads only when the row is 16-byte aligned
-  for (int c = tid; c < nvec; c += blockDim.x) {
-    float f[8];
-    unpack8<T>(ldg_stream(p + (size_t)c * 8), f);
+  int const nthr = blockDim.x;
+  for (int c0 = tid; c0 < nvec; c0 += 4 * nthr) { // four independent 128-bit loads in flight per thread
+    uint4 v[4];
 #pragma unroll
-    for (int e = 0; e < 8; e++) { // increasing index inside a thread: strict > keeps the first maximum
-      if (f[e] > best || (f[e] == best && c * 8 + e < bi)) {
-        best = f[e];
-        bi = c * 8 + e;
+    for (int u = 0; u < 4; u++) {
+      int const c = c0 + u * nthr;
+      v[u] = c < nvec ? ldg_stream(p + (size_t)c * 8) : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      int const c = c0 + u * nthr;
+      if (c < nvec) {
+        float f[8];
+        unpack8<T>(v[u], f);
+#pragma unroll
+        for (int e = 0; e < 8; e++) { // increasing index inside a thread: strict > keeps the first maximum
+          if (f[e] > best || (f[e] == best && c * 8 + e < bi)) {
+            best = f[e];
+            bi = c * 8 + e;
+          }
+        }
       }
     }
   }
@@ -245,7 +258,8 @@ int ffb_argmax(void const *input_dev, int *indices_dev, float *prob_dev, int *pa
   if (num_tokens == 0) {
     return FFB_OK;
   }
-  int const threads = length >= 8192 ? 1024 : 256;
+  // few rows: 1024 threads per row (latency); many rows: 256, so that every row's CTA is resident in one wave
+  int const threads = (length >= 8192 && num_tokens <= 2 * kNumSMs) ? 1024 : 256;
   if (dtype == FFB_DT_HALF) {
     argmax_kernel<__half><<<num_tokens, threads, 0, (cudaStream_t)stream>>>((__half const *)input_dev, indices_dev,
                                                                             prob_dev, parent_dev, length);
