@@ -53,7 +53,8 @@ __device__ __forceinline__ __half dq_elem(int q, DqCoefHalf const &c) {
 // Same roundings, cheaper instructions:
 //   * float(q): m = 0x4B000000 | q is the float 2^23 + q, and fma(rcp, m, -rcp * 2^23) rounds the exact product
 //     rcp * q once - the value FMUL(rcp, float(q)) gives (-rcp * 2^23 is exact: a power-of-two scaling).  Needs a
-//     finite rcp; dq_pair_ok() says so and the callers fall back to dq_elem otherwise (scale = 0, NaN).
+//     finite, non-negative rcp; dq_pair_ok() says so and the callers fall back to dq_elem otherwise (scale = 0, NaN,
+//     negative scales: sign of a zero quotient).
 //   * one cvt.rn.f16x2.f32 rounds both quotients, one HADD2 adds both offsets (adjacent in the blob).
 //   * __hdiv's correction step runs only for 0 < |quotient| < 0x008F (8.5e-6).  With q >= 1 that needs
 //     |rcp| < 8.5e-6, i.e. |scale| > 117000: no half is that large (max 65504; scale = inf gives rcp = 0 and the
@@ -64,9 +65,13 @@ struct DqPairHalf {
   float r0, c0, r1, c1; // rcp.approx.ftz(scale) and -rcp * 2^23 of two neighbouring columns
   uint32_t off2;        // their offsets as stored (half2)
 };
-__device__ __forceinline__ bool dq_pair_ok(DqPairHalf const &c) { // both reciprocals finite
-  return ((__float_as_uint(c.r0) & 0x7F800000u) != 0x7F800000u) && ((__float_as_uint(c.r1) & 0x7F800000u) != 0x7F800000u);
-}
+// Both reciprocals finite AND non-negative (one unsigned compare each: a set sign bit is above 0x7F800000 too).
+// Negative scales take the element-wise rule: with q = 0 the reference's product rcp * 0 is -0 for a negative rcp,
+// while fma(rcp, 2^23, -rcp * 2^23) cancels exactly to +0, and the two differ after the add when the offset is -0
+// (found by running the reference's own kernel on the same blobs, tests/test_gpu_linear.py; compress() never
+// produces a negative scale, so real checkpoints stay on the pair rule).
+__device__ __forceinline__ bool dq_rcp_ok(float r) { return __float_as_uint(r) < 0x7F800000u; }
+__device__ __forceinline__ bool dq_pair_ok(DqPairHalf const &c) { return dq_rcp_ok(c.r0) && dq_rcp_ok(c.r1); }
 __device__ __forceinline__ DqPairHalf dq_pair_coef(__half s0, __half s1, uint32_t off2) {
   DqPairHalf c;
   c.r0 = rcp_approx_ftz(__half2float(s0));

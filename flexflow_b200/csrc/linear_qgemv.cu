@@ -18,7 +18,7 @@
 //   * shared-memory wavefronts are what a lane's bytes cost, broadcast or not (a 128-bit load is served per quarter
 //     warp), so the staged coefficient is the reciprocal alone (4 B per column; -rcp * 2^23 is one FMUL in the lane)
 //     and the value rows are padded so that every wavefront is conflict-free;
-//   * a scale of zero (rcp = inf) switches the stage to the element-wise rule (block-wide OR folded into the
+//   * a zero or negative scale (rcp = inf, or the sign of a zero quotient) switches the stage to the element-wise rule (block-wide OR folded into the
 //     per-stage barrier);
 //   * the 16 k-slices of a tile are summed in warp order (deterministic).
 #include <cstdlib>
@@ -215,7 +215,7 @@ linear_qgemv_kernel(__half const *__restrict__ A, uint8_t const *__restrict__ W,
     c.x = rcp_approx_ftz(__low2float(h2));
     c.y = rcp_approx_ftz(__high2float(h2));
     *reinterpret_cast<float2 *>(coef + b * QG_KS + 2 * tid) = c;
-    return (((__float_as_uint(c.x) & 0x7F800000u) == 0x7F800000u) || ((__float_as_uint(c.y) & 0x7F800000u) == 0x7F800000u)) ? 1 : 0;
+    return (dq_rcp_ok(c.x) && dq_rcp_ok(c.y)) ? 0 : 1; // inf / NaN / negative: element-wise rule for this stage
   };
 
   int bad_cur = 0;

@@ -21,6 +21,28 @@ def build(force=False):
     return _SO
 
 
+_REF_SO = os.path.join(_HERE, "_ref", "libref_decompress.so")
+_ref = None
+
+
+def build_ref():
+    """Compile the reference's own decompression kernels (oracle/Makefile target `ref`) where /root/reference is
+    mounted; elsewhere (the GPU box) the prebuilt oracle/_ref/*.so that travelled with the snapshot is used."""
+    if os.path.isdir("/root/reference/src/ops/kernels"):
+        subprocess.run(["make", "-C", _HERE, "-s", "ref"], check=True)
+    return _REF_SO if os.path.exists(_REF_SO) else None
+
+
+def ref_lib():
+    """The reference's decompress kernels compiled for sm_100a (GPU only), or None when the .so was not built."""
+    global _ref
+    if _ref is None and os.path.exists(_REF_SO):
+        _ref = C.CDLL(_REF_SO)
+        for n in ("ref_decompress_int4_half", "ref_decompress_int8_half"):
+            getattr(_ref, n).argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    return _ref
+
+
 def lib():
     global _lib
     if _lib is None:

@@ -1,4 +1,6 @@
 """GPU parity: int4/int8 decompression (bit-exact) and the projection GEMMs vs the CPU oracle."""
+import ctypes as C
+
 import numpy as np
 import pytest
 
@@ -278,3 +280,76 @@ def test_linear_qgemv_zero_scale_takes_the_elementwise_rule(quant, monkeypatch):
         assert (got[k0][:, ok] == want[ok, k0:k0 + 16].T).all(), k0
         g1 = got[k0][:, 32:64].view(np.float16)
         assert not np.isfinite(g1).any()  # inf, or 0 * inf = NaN, in every dot product of the group
+
+
+# ---- the reference's OWN decompress kernels (oracle/_ref/libref_decompress.so, compiled from
+# /root/reference/src/ops/kernels/decompress_kernels.cu by oracle/Makefile) run on the same GPU ----
+
+def _ref_dequant(blob_dev, bits, in_dim, out_dim):
+    torch = _torch()
+    ref = O.ref_lib()
+    out = torch.empty(out_dim, in_dim, dtype=torch.float16, device="cuda")
+    fn = ref.ref_decompress_int4_half if bits == 4 else ref.ref_decompress_int8_half
+    rc = fn(C.c_void_p(blob_dev.data_ptr()), C.c_void_p(out.data_ptr()), in_dim, out_dim,
+            C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    torch.cuda.synchronize()
+    return out
+
+
+needs_ref = pytest.mark.skipif(O.ref_lib() is None, reason="oracle/_ref/libref_decompress.so not built (make -C oracle ref)")
+
+
+@needs_ref
+@pytest.mark.parametrize("bits", [4, 8])
+@pytest.mark.parametrize("shape", [(12288, 4096), (4096, 4096), (11008, 4096), (4096, 11008)])
+def test_dequant_bit_exact_against_the_reference_kernel(bits, shape):
+    """the four LLaMA-2-7B weight shapes, random values and random fp16 scales / offsets of both
+    signs and all magnitudes a compress() blob can hold; ffb_dequant_* == the reference kernel, every bit."""
+    torch = _torch()
+    from flexflow_b200 import ops
+    out_dim, in_dim = shape
+    g = torch.Generator(device="cuda").manual_seed(bits * 1000 + out_dim)
+    n = in_dim * out_dim
+    vals = torch.randint(0, 256, (n * bits // 8,), generator=g, device="cuda", dtype=torch.uint8)
+    sc = (torch.randn(n // 32, generator=g, device="cuda") * torch.exp(6 * torch.randn(n // 32, generator=g, device="cuda"))).half()
+    sc[sc == 0] = 1.0  # zero scales have their own test below
+    of = (torch.randn(n // 32, generator=g, device="cuda") * 0.1).half()
+    of[::13] = -0.0  # with q = 0 and a negative scale the reference gives -0 + -0 = -0 (sign of the zero quotient)
+    of[5::13] = 0.0
+    vals[::7] = 0
+    blob = torch.cat([vals, of.view(torch.uint8), sc.view(torch.uint8)])
+    want = _ref_dequant(blob, bits, in_dim, out_dim)
+    got = ops.decompress_weights(blob, in_dim, out_dim, B.DT_INT4 if bits == 4 else B.DT_INT8)
+    torch.cuda.synchronize()
+    assert torch.equal(got.view(torch.int16), want.view(torch.int16))
+
+
+@needs_ref
+@pytest.mark.parametrize("bits", [4, 8])
+def test_oracle_and_kernels_agree_with_the_reference_kernel_on_edge_scales(bits):
+    """Pins the CPU oracle itself: oracle == reference kernel == ffb_dequant on a blob whose scales sweep every finite
+    half (zero, subnormals, both signs, inf) and whose offsets include inf."""
+    torch = _torch()
+    from flexflow_b200 import ops
+    in_dim, out_dim = 65536 // 8, 32 * 8  # 65536 groups-columns: one per half bit pattern
+    n = in_dim * out_dim
+    rng = np.random.default_rng(bits)
+    vals = rng.integers(0, 256, n * bits // 8, dtype=np.uint8)
+    sc = np.arange(65536, dtype=np.uint16)
+    sc = sc[~np.isnan(sc.view(np.float16))]  # NaN payload propagation is not part of the contract
+    sc = np.resize(sc, n // 32)
+    of = (rng.standard_normal(n // 32) * 0.1).astype(np.float16)
+    of[::997] = np.inf
+    of[1::5] = -0.0
+    of[2::5] = 0.0
+    vals[::3] = 0
+    blob = np.concatenate([vals, of.view(np.uint8), sc.view(np.uint8)])
+    bdev = torch.from_numpy(blob).cuda()
+    want = _ref_dequant(bdev, bits, in_dim, out_dim).cpu().numpy().view(np.uint16)
+    got = ops.decompress_weights(bdev, in_dim, out_dim, B.DT_INT4 if bits == 4 else B.DT_INT8).cpu().numpy().view(np.uint16)
+    orc = O.dequant(blob, bits, in_dim, out_dim).view(np.uint16)
+    nan_w = np.isnan(want.view(np.float16))
+    for name, x in (("kernel", got), ("oracle", orc)):
+        assert (np.isnan(x.view(np.float16)) == nan_w).all(), name
+        assert (x[~nan_w] == want[~nan_w]).all(), name

@@ -73,7 +73,7 @@ def main():
     def decode7b():
         lens = {s: 2047 for s in range(16)}
         return TL.make_inc_batch([dict(slot=s, first_depth=2047, ntok=1) for s in range(16)]), lens
-    if only != "cfg4":
+    if only not in ("cfg4", "cfg5"):
         res.append(run("cfg2 7B decode b16 ctx2048", B.INC_DECODING_MODE, 32, 32, 128, decode7b, 16, 2048, 16))
     if only == "cfg2":
         return
@@ -86,15 +86,19 @@ def main():
         return f
     if only != "cfg4" or True:
         pass
-    res.append(run("cfg4 7B tree-verify b8 x64 ctx1024", B.TREE_VERIFY_MODE, 32, 32, 128, tree7b(64), 8, int(os.environ.get("FFB_BENCH_CTX", "1024")) + 76, 512))
+    if only != "cfg5":
+        res.append(run("cfg4 7B tree-verify b8 x64 ctx1024", B.TREE_VERIFY_MODE, 32, 32, 128, tree7b(64), 8, int(os.environ.get("FFB_BENCH_CTX", "1024")) + 76, 512))
     if only == "cfg4":
         return
-    res.append(run("cfg4' 7B tree-verify b8 x25 ctx1024 (reference max tree)", B.TREE_VERIFY_MODE, 32, 32, 128, tree7b(25), 8, 1100, 512))
+    if only != "cfg5":
+        res.append(run("cfg4' 7B tree-verify b8 x25 ctx1024 (reference max tree)", B.TREE_VERIFY_MODE, 32, 32, 128, tree7b(25), 8, 1100, 512))
 
     def tree70b():
         lens = {s: 4096 for s in range(32)}
         return TL.make_tree_batch([dict(slot=s, committed_len=4096, parent=TL.random_tree(rng, 32)) for s in range(32)]), lens
     res.append(run("cfg5 70B tree-verify b32 x32 ctx4096, TP=8 shard (8q/1kv)", B.TREE_VERIFY_MODE, 8, 1, 128, tree70b, 32, 4200, 1024, layers=8))
+    if only == "cfg5":
+        return
 
     def prompt7b():
         return TL.make_inc_batch([dict(slot=0, first_depth=0, ntok=1024, prompt=True)]), {0: 0}

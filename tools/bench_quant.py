@@ -8,6 +8,7 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from flexflow_b200 import batch_config as B  # noqa: E402
+from flexflow_b200 import lib as L  # noqa: E402
 from flexflow_b200 import ops  # noqa: E402
 from tools.bench_linear import time_ms  # noqa: E402
 
@@ -47,6 +48,37 @@ def main():
             res.append(dict(layer=lname, quant=name, M=M, us=ms * 1e3, blob_mb=blobs[0].numel() / 1e6,
                             blob_gbs=blobs[0].numel() / ms / 1e6))
             print(res[-1], flush=True)
+            del blobs
+    # standalone decompression (what the reference runs before every GEMM when weights are offloaded,
+    # src/ops/kernels/linear_kernels.cu:464-490): ours against the reference's own kernel compiled for sm_100a
+    if not only and not only_layer:
+        import ctypes as C
+        from oracle import oracle as O  # the checker's loader of oracle/_ref (bench tools may use it)
+        ref = O.ref_lib()
+        K, N = 4096, 12288
+        for name, qt, bits in (("int8", B.DT_INT8, 8), ("int4", B.DT_INT4, 4)):
+            blobs = [make_blob(K, N, bits, gen) for _ in range(4)]
+            out = torch.empty(N, K, dtype=torch.float16, device="cuda")
+            i = [0]
+            fn_ours = (L.load().ffb_dequant_int8 if bits == 8 else L.load().ffb_dequant_int4)
+
+            def ours():
+                i[0] += 1
+                fn_ours(C.c_void_p(blobs[i[0] % 4].data_ptr()), C.c_void_p(out.data_ptr()), K, N, B.DT_HALF,
+                        C.c_void_p(torch.cuda.current_stream().cuda_stream))
+            row = dict(layer="qkv_proj dequant only", quant=name, ours_us=time_ms(ours, iters=12) * 1e3,
+                       bytes_mb=(blobs[0].numel() + 2 * K * N) / 1e6)
+            row["ours_gbs"] = row["bytes_mb"] / row["ours_us"] * 1e3
+            if ref is not None:
+                fn_ref = ref.ref_decompress_int8_half if bits == 8 else ref.ref_decompress_int4_half
+
+                def theirs():
+                    i[0] += 1
+                    fn_ref(C.c_void_p(blobs[i[0] % 4].data_ptr()), C.c_void_p(out.data_ptr()), K, N,
+                           C.c_void_p(torch.cuda.current_stream().cuda_stream))
+                row["reference_kernel_us"] = time_ms(theirs, iters=12) * 1e3
+            res.append(row)
+            print(row, flush=True)
             del blobs
     if "--json" in sys.argv:
         json.dump(res, open(sys.argv[sys.argv.index("--json") + 1], "w"), indent=1)
