@@ -43,6 +43,20 @@ def ref_lib():
     return _ref
 
 
+_REF_ATTN_SO = os.path.join(_HERE, "_ref", "libref_attn.so")
+_ref_attn = None
+
+
+def ref_attn_lib():
+    """The reference's decode attention kernel (inc_multihead_self_attention.cu:372-623) compiled for sm_100a, or None."""
+    global _ref_attn
+    if _ref_attn is None and os.path.exists(_REF_ATTN_SO):
+        _ref_attn = C.CDLL(_REF_ATTN_SO)
+        _ref_attn.ref_inc_generation_half.argtypes = [C.c_void_p] * 4 + [C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                                                        C.c_int, C.c_int, C.c_void_p]
+    return _ref_attn
+
+
 def lib():
     global _lib
     if _lib is None:

@@ -1,0 +1,74 @@
+// ref_attn_wrap.cu — compiles the REFERENCE's own decode attention kernel,
+// compute_attention_kernel_generation_kernel (/root/reference/src/ops/inc_multihead_self_attention.cu:372-623), with the
+// reference's own headers (flexflow/batch_config.h, flexflow/ops/kernels/inc_multihead_self_attention_utils.cuh, read
+// where they lie) into oracle/_ref/libref_attn.so.  TEST INFRASTRUCTURE ONLY: the GPU tests compare ffb_inc_attn_forward
+// with it on the same inputs and tools/bench_attn.py times it beside ours.  Nothing is copied into this repository:
+// the Makefile streams the kernel's text (from its `__global__` line to its closing brace) into a temporary file that
+// is included below and deleted after the compile.  The rest of that .cu needs Legion-typed Metas, accessors, cuBLAS
+// and cuDNN handles and is not buildable here.
+//
+// Supplied here instead of the .cu's surroundings: the template header of the kernel (:372-377), WARP_SIZE (:30),
+// QKV_WEIGHT_NUM (flexflow/ops/kernels/inc_multihead_self_attention_kernels.h:4) and the launch, which restates
+// LAUNCH_ATTENTION_SCORE_KERNEL / compute_attention_kernel_generation (:880-927): grid (num_q_heads,
+// num_generation_tokens), 128 threads, THREADS_PER_KEY 4, THREADS_PER_VALUE Dh * sizeof(DT) / 16, dynamic shared memory
+// smem_size_in_bytes<DT>(Dh, max_sequence_length, THREADS_PER_VALUE, 128).
+#include <cassert>
+#include <cfloat>
+#include <cstdint>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <math_constants.h>
+
+#include "flexflow/batch_config.h"
+#include "flexflow/ops/kernels/inc_multihead_self_attention_utils.cuh"
+
+#define WARP_SIZE 32
+#define QKV_WEIGHT_NUM 3
+
+namespace FlexFlow {
+namespace Kernels {
+namespace IncMultiHeadAttention {
+
+template <typename DT, int THREADS_PER_BLOCK, int Dh, int Dh_MAX, int THREADS_PER_KEY, int THREADS_PER_VALUE>
+#include REF_GEN_KERNEL_INC
+
+template <int Dh>
+static int launch_half(void const *qkv, void const *kc, void const *vc, void *out, float scale, int max_seq, int hidden,
+                       void *request_infos, int num_q_heads, int num_gen_tokens, cudaStream_t stream) {
+  constexpr int TPV = threads_per_value_t<half, Dh>::value;
+  size_t const smem = smem_size_in_bytes<half>(Dh, max_seq, TPV, 128);
+  auto kern = compute_attention_kernel_generation_kernel<half, 128, Dh, Dh, 4, TPV>;
+  if (smem > 48 * 1024) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  }
+  dim3 grid(num_q_heads, num_gen_tokens);
+  kern<<<grid, 128, smem, stream>>>((half const *)qkv, (half const *)kc, (half const *)vc, (half *)out, scale, max_seq,
+                                    Dh, hidden, (BatchConfig::PerRequestInfo *)request_infos);
+  return (int)cudaGetLastError();
+}
+
+} // namespace IncMultiHeadAttention
+} // namespace Kernels
+} // namespace FlexFlow
+
+extern "C" {
+
+// query: devQKVProjArray [tokens][3][hidden] (generation tokens first); key/value cache: [request][max_seq][hidden];
+// request_infos: device copy of BatchConfig::requestsInfo.  Returns a cudaError_t.
+int ref_inc_generation_half(void const *qkv, void const *key_cache, void const *value_cache, void *out, float scale,
+                            int max_seq, int head_dim, int hidden, void *request_infos_dev, int num_q_heads,
+                            int num_gen_tokens, void *stream) {
+  using namespace FlexFlow::Kernels::IncMultiHeadAttention;
+  if (head_dim == 128) {
+    return launch_half<128>(qkv, key_cache, value_cache, out, scale, max_seq, hidden, request_infos_dev, num_q_heads,
+                            num_gen_tokens, (cudaStream_t)stream);
+  }
+  if (head_dim == 64) {
+    return launch_half<64>(qkv, key_cache, value_cache, out, scale, max_seq, hidden, request_infos_dev, num_q_heads,
+                           num_gen_tokens, (cudaStream_t)stream);
+  }
+  return -1;
+}
+int ref_sizeof_per_request_info(void) { return (int)sizeof(FlexFlow::BatchConfig::PerRequestInfo); }
+
+} // extern "C"

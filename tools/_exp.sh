@@ -1,2 +1,2 @@
-timeout 900 python -m pytest tests/test_gpu_linear.py -x -q --timeout 300 2>&1 | tail -5
-timeout 200 python tools/bench_quant.py --json gpurun_out/bench_quant.json 2>&1 | grep -v Warn | tail -6
+timeout 600 python -m pytest tests/test_gpu_attn_ref.py -x -q --timeout 300 2>&1 | tail -8
+timeout 300 python tools/bench_attn.py --only cfg2 2>&1 | tail -3

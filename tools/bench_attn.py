@@ -65,6 +65,45 @@ def run(name, mode, nq, nkv, dh, reqs_fn, max_req, max_seq, max_tok, layers=6, i
     return r
 
 
+def reference_decode_kernel_ms(nq=32, dh=128, nreq=16, ctx=2048, layers=4, iters=10):
+    """The reference's own decode kernel (oracle/_ref/libref_attn.so, built from the reference tree) at the configs[1]
+    shapes: `layers` distinct caches in the reference layout [request][max_seq][hidden] so that the working set exceeds
+    L2, CUDA events around back-to-back launches."""
+    import ctypes as C
+    from oracle import oracle as O  # loader of oracle/_ref only; the checker is not on the product path
+    ref = O.ref_attn_lib()
+    if ref is None:
+        return None
+    H = nq * dh
+    g = torch.Generator(device="cuda").manual_seed(1)
+    caches = [(torch.randn(nreq, ctx, H, generator=g, device="cuda", dtype=torch.float16),
+               torch.randn(nreq, ctx, H, generator=g, device="cuda", dtype=torch.float16)) for _ in range(layers)]
+    bc = TL.make_inc_batch([dict(slot=s, first_depth=ctx - 1, ntok=1) for s in range(nreq)])
+    ri = torch.from_numpy(np.frombuffer(bytes(bc.requestsInfo), dtype=np.uint8).copy()).cuda()
+    qkv = torch.randn(nreq, 3, H, generator=g, device="cuda", dtype=torch.float16)
+    out = torch.empty(nreq, H, device="cuda", dtype=torch.float16)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def launch(kc, vc):
+        rc = ref.ref_inc_generation_half(C.c_void_p(qkv.data_ptr()), C.c_void_p(kc.data_ptr()), C.c_void_p(vc.data_ptr()),
+                                         C.c_void_p(out.data_ptr()), 1.0 / np.sqrt(dh), ctx, dh, H, C.c_void_p(ri.data_ptr()),
+                                         nq, nreq, st)
+        assert rc == 0
+    for kc, vc in caches:
+        launch(kc, vc)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda._sleep(2_000_000)
+    e0.record()
+    for _ in range(iters):
+        for kc, vc in caches:
+            launch(kc, vc)
+    e1.record()
+    torch.cuda.synchronize()
+    assert torch.isfinite(out.float()).all()
+    return e0.elapsed_time(e1) / (iters * layers)
+
+
 def main():
     rng = np.random.default_rng(0)
     res = []
@@ -75,6 +114,11 @@ def main():
         return TL.make_inc_batch([dict(slot=s, first_depth=2047, ntok=1) for s in range(16)]), lens
     if only not in ("cfg4", "cfg5"):
         res.append(run("cfg2 7B decode b16 ctx2048", B.INC_DECODING_MODE, 32, 32, 128, decode7b, 16, 2048, 16))
+        ref_ms = reference_decode_kernel_ms()
+        if ref_ms is not None:
+            res[-1]["reference_kernel_ms"] = ref_ms
+            res[-1]["speedup_vs_reference_kernel"] = ref_ms / res[-1]["kernel_ms"]
+            print("reference decode kernel (compiled from the reference tree, same GPU): %.1f us -> x%.2f" % (ref_ms * 1e3, ref_ms / res[-1]["kernel_ms"]), flush=True)
     if only == "cfg2":
         return
 
