@@ -15,6 +15,7 @@
 #include <cassert>
 #include <cfloat>
 #include <cstdint>
+#include <cuComplex.h>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <math_constants.h>
@@ -31,6 +32,14 @@ namespace IncMultiHeadAttention {
 
 template <typename DT, int THREADS_PER_BLOCK, int Dh, int Dh_MAX, int THREADS_PER_KEY, int THREADS_PER_VALUE>
 #include REF_GEN_KERNEL_INC
+
+// apply_rotary_embedding_hf (:664-738): the text from its name line to its closing brace; `template <typename DT>
+// __global__ void` (:664-665) supplied here.  CUDA_KERNEL_LOOP as in include/flexflow/utils/cuda_helper.h:64-66.
+#define CUDA_KERNEL_LOOP(i, n) \
+  for (Legion::coord_t i = blockIdx.x * blockDim.x + threadIdx.x; i < (n); i += blockDim.x * gridDim.x)
+template <typename DT>
+__global__ void
+#include REF_ROPE_KERNEL_INC
 
 template <int Dh>
 static int launch_half(void const *qkv, void const *kc, void const *vc, void *out, float scale, int max_seq, int hidden,
@@ -69,6 +78,25 @@ int ref_inc_generation_half(void const *qkv, void const *key_cache, void const *
   }
   return -1;
 }
+// compute_qkv_kernel's RoPE step (:838-857): in place on devQKVProjArray [tokens][3][hidden]; complex_scratch holds
+// tokens * hidden cuFloatComplex; token_infos_dev is a device copy of BatchConfig::tokensInfo.
+int ref_apply_rotary_embedding_half(void *qkv, void *complex_scratch, void const *token_infos_dev, float rope_theta,
+                                    int llama3, float factor, float low_freq_factor, float high_freq_factor,
+                                    int original_max_position_embeddings, int proj_size, int num_tokens, int hidden,
+                                    void *stream) {
+  using namespace FlexFlow;
+  int const parallelism = num_tokens * hidden;
+  int blocks = (parallelism + 1023) / 1024;
+  blocks = blocks > 32768 ? 32768 : blocks;
+  size_t const q_array_size = (size_t)num_tokens * hidden; // qProjSize * num_tokens * num_q_heads
+  Kernels::IncMultiHeadAttention::apply_rotary_embedding_hf<half>
+      <<<blocks, parallelism < 1024 ? parallelism : 1024, 0, (cudaStream_t)stream>>>(
+          (half *)qkv, (cuFloatComplex *)complex_scratch, (BatchConfig::PerTokenInfo const *)token_infos_dev, rope_theta,
+          llama3 != 0, factor, low_freq_factor, high_freq_factor, original_max_position_embeddings, proj_size, proj_size,
+          num_tokens, q_array_size, hidden);
+  return (int)cudaGetLastError();
+}
+int ref_sizeof_per_token_info(void) { return (int)sizeof(FlexFlow::BatchConfig::PerTokenInfo); }
 int ref_sizeof_per_request_info(void) { return (int)sizeof(FlexFlow::BatchConfig::PerRequestInfo); }
 
 } // extern "C"

@@ -63,3 +63,48 @@ def test_decode_attention_against_the_reference_kernel(dh, nq, lens):
     assert TL.rel_err(got, ref) < 1e-2, TL.rel_err(got, ref)
     # and the oracle restates that kernel: closer to it than the product needs to be
     assert TL.rel_err(orc, ref) < 2e-3, TL.rel_err(orc, ref)
+
+
+@needs_ref
+@pytest.mark.parametrize("dh,nq,llama3", [(128, 8, False), (64, 12, False), (128, 4, True)])
+def test_rope_kv_append_and_decode_against_the_reference_kernels(dh, nq, llama3):
+    """The whole decode chain with RoPE on: the reference's apply_rotary_embedding_hf (inc_...cu:664-738) rotates a
+    copy of the projection output in place; its rotated K must be what the product appended to its cache, and the
+    reference decode kernel fed with the rotated queries must reproduce the product's output."""
+    import torch
+    from gpu_harness import Pair, make_qkv
+    rng = np.random.default_rng(dh * 3 + nq)
+    lens = {0: 17, 2: 511, 3: 1999, 6: 4}
+    max_requests, max_seq = 8, 2048
+    p = Pair(B.INC_DECODING_MODE, "half", nq, nq, dh, max_requests, max_seq, 64, apply_rope=True, llama3=llama3)
+    for slot, n in lens.items():
+        p.fill_cache(rng, slot, n)
+    bc = TL.make_inc_batch([dict(slot=s, first_depth=n, ntok=1) for s, n in lens.items()])
+    T, H = len(lens), nq * dh
+    qkv = make_qkv(rng, T, nq, nq, dh, "half")
+    got, orc = p.forward_both(bc, qkv)
+
+    ref = O.ref_attn_lib()
+    assert ref.ref_sizeof_per_token_info() == C.sizeof(B.PerTokenInfo)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    rot = torch.from_numpy(np.ascontiguousarray(qkv, dtype=np.float32)).to("cuda", torch.float16).contiguous()
+    scratch = torch.empty(T * H * 2, dtype=torch.float32, device="cuda")
+    ti = torch.from_numpy(np.frombuffer(bytes(bc.tokensInfo), dtype=np.uint8).copy()).cuda()
+    rc = ref.ref_apply_rotary_embedding_half(C.c_void_p(rot.data_ptr()), C.c_void_p(scratch.data_ptr()),
+                                             C.c_void_p(ti.data_ptr()), 10000.0, int(llama3), 8.0, 1.0, 4.0, 8192, dh, T, H, st)
+    assert rc == 0
+    torch.cuda.synchronize()
+    rot_k = rot[:, 1].float().cpu().numpy().reshape(T, nq, dh)
+    # 1. RoPE + KV placement: the row the product appended at abs_depth is the reference's rotated K (and the raw V)
+    exact = []
+    for t, (slot, n) in enumerate(sorted(lens.items())):
+        k, v = p.m.read_kv(slot, n, 1)
+        kk = k.float().cpu().numpy()[0]
+        exact.append(kk == rot_k[t])
+        np.testing.assert_allclose(kk, rot_k[t], rtol=2e-3, atol=2e-3)
+        assert np.array_equal(v.float().cpu().numpy()[0].reshape(-1), qkv[t, 2].astype(np.float32))
+    assert np.mean(exact) > 0.97, np.mean(exact)  # same expression; sin / cos of the two compilations agree to the last bit almost everywhere
+    # 2. attention on the rotated queries
+    out_ref = _reference_decode(p, bc, rot, lens, max_requests, max_seq)
+    assert TL.rel_err(got, out_ref) < 1e-2, TL.rel_err(got, out_ref)
+    assert TL.rel_err(orc, out_ref) < 2e-3, TL.rel_err(orc, out_ref)
