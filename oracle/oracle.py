@@ -60,6 +60,22 @@ def ref_attn_lib():
     return _ref_attn
 
 
+_REF_NORM_SO = os.path.join(_HERE, "_ref", "libref_norm.so")
+_ref_norm = None
+
+
+def ref_norm_lib():
+    """The reference's (Residual)RMSNorm forward kernels and ArgMax's cub call compiled for sm_100a, or None."""
+    global _ref_norm
+    if _ref_norm is None and os.path.exists(_REF_NORM_SO):
+        _ref_norm = C.CDLL(_REF_NORM_SO)
+        _ref_norm.ref_residual_rms_norm_half.argtypes = [C.c_void_p] * 7 + [C.c_int, C.c_int, C.c_float, C.c_void_p]
+        _ref_norm.ref_rms_norm_half.argtypes = [C.c_void_p] * 5 + [C.c_int, C.c_int, C.c_float, C.c_void_p]
+        _ref_norm.ref_argmax_half.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                              C.c_size_t, C.POINTER(C.c_size_t), C.c_void_p, C.c_void_p]
+    return _ref_norm
+
+
 def lib():
     global _lib
     if _lib is None:

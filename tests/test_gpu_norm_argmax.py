@@ -115,3 +115,65 @@ def test_norm_wrappers_mirror_reference_names():
     want_res, want = O.residual_rms_norm(a.cpu().numpy().view(np.uint16), b.cpu().numpy().view(np.uint16),
                                          w.cpu().numpy().view(np.uint16), 1e-5, "half")
     assert (out.cpu().numpy().view(np.uint16) == want).all(axis=1).mean() >= 0.9
+
+
+# ---- against the reference's OWN kernels (oracle/_ref/libref_norm.so, compiled from the reference tree) ----
+needs_ref = pytest.mark.skipif(O.ref_norm_lib() is None, reason="oracle/_ref/libref_norm.so not built (make -C oracle ref)")
+
+
+@needs_ref
+@pytest.mark.parametrize("n", [64, 768, 4096, 5120, 8192])
+@pytest.mark.parametrize("residual", [False, True])
+def test_rms_norm_equals_the_reference_kernel_bit_for_bit(n, residual):
+    """Same roundings, same summation order, same rsqrtf on the same GPU: every bit of every row."""
+    torch = _torch()
+    ref = O.ref_norm_lib()
+    rng = np.random.default_rng(n + residual)
+    rows = 131
+    x1 = O.to_bits(rng.standard_normal((rows, n)).astype(np.float32) * 2.0, "half")
+    x2 = O.to_bits(rng.standard_normal((rows, n)).astype(np.float32), "half") if residual else None
+    w = O.to_bits(1.0 + 0.2 * rng.standard_normal(n).astype(np.float32), "half")
+    res, got = _gpu_norm(x1, x2, w, 1e-5, "half")
+    d1, dw = _dev_bits(x1), _dev_bits(w)
+    out, rms, norm = torch.zeros_like(d1), torch.zeros(rows, dtype=torch.int16, device="cuda"), torch.zeros_like(d1)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    if residual:
+        d2, rout = _dev_bits(x2), torch.zeros_like(d1)
+        assert ref.ref_residual_rms_norm_half(p(d1), p(d2), p(dw), p(rout), p(out), p(rms), p(norm), rows, n, 1e-5, st) == 0
+        torch.cuda.synchronize()
+        assert np.array_equal(res, rout.cpu().numpy().view(np.uint16))
+    else:
+        assert ref.ref_rms_norm_half(p(d1), p(dw), p(out), p(rms), p(norm), rows, n, 1e-5, st) == 0
+        torch.cuda.synchronize()
+    assert np.array_equal(got, out.cpu().numpy().view(np.uint16))
+
+
+@needs_ref
+@pytest.mark.parametrize("shape", [(16, 32000), (64, 32000), (7, 50257)])
+def test_argmax_equals_the_reference_cub_call(shape):
+    torch = _torch()
+    from flexflow_b200 import ops
+    ref = O.ref_norm_lib()
+    rows, v = shape
+    g = torch.Generator(device="cuda").manual_seed(rows)
+    x = torch.randn(rows, v, generator=g, device="cuda").half()
+    x[0, 11] = x[0, v - 3] = 30.0   # ties resolve to the smaller index in both
+    offs = (torch.arange(rows + 1, device="cuda", dtype=torch.int32) * v).contiguous()
+    kv = torch.zeros(rows * 2, dtype=torch.int64, device="cuda")
+    need = C.c_size_t(0)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    assert ref.ref_argmax_half(C.c_void_p(x.data_ptr()), None, None, rows, C.c_void_p(offs.data_ptr()), None, 0,
+                               C.byref(need), C.c_void_p(kv.data_ptr()), st) == 0
+    tmp = torch.zeros(max(need.value, 16), dtype=torch.uint8, device="cuda")
+    want_idx = torch.full((rows,), -1, dtype=torch.int32, device="cuda")
+    want_prob = torch.zeros(rows, dtype=torch.float32, device="cuda")
+    assert ref.ref_argmax_half(C.c_void_p(x.data_ptr()), C.c_void_p(want_idx.data_ptr()), C.c_void_p(want_prob.data_ptr()),
+                               rows, C.c_void_p(offs.data_ptr()), C.c_void_p(tmp.data_ptr()), need.value, None,
+                               C.c_void_p(kv.data_ptr()), st) == 0
+    idx = torch.full((rows,), -1, dtype=torch.int32, device="cuda")
+    parent = torch.full((rows,), -1, dtype=torch.int32, device="cuda")
+    probs = ops.ArgMax.forward_kernel_wrapper(ops.ArgMaxMeta(None, beam_search=True), None, x, idx, parent, rows)
+    torch.cuda.synchronize()
+    assert torch.equal(idx, want_idx) and int(idx[0]) == 11
+    assert torch.equal(probs, want_prob)
