@@ -54,6 +54,8 @@ def ref_attn_lib():
         _ref_attn = C.CDLL(_REF_ATTN_SO)
         _ref_attn.ref_inc_generation_half.argtypes = [C.c_void_p] * 4 + [C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                                                         C.c_int, C.c_int, C.c_void_p]
+        _ref_attn.ref_spec_generation_half.argtypes = [C.c_void_p] * 4 + [C.c_float, C.c_int, C.c_int, C.c_int] + \
+            [C.c_void_p] * 4 + [C.c_int, C.c_int, C.c_void_p]
         _ref_attn.ref_apply_rotary_embedding_half.argtypes = [C.c_void_p] * 3 + [C.c_float, C.c_int, C.c_float, C.c_float,
                                                                                  C.c_float, C.c_int, C.c_int, C.c_int,
                                                                                  C.c_int, C.c_void_p]

@@ -41,6 +41,30 @@ template <typename DT>
 __global__ void
 #include REF_ROPE_KERNEL_INC
 
+// compute_spec_inc_attention_kernel_generation_kernel (src/ops/spec_inc_multihead_self_attention.cu:36-309), same
+// template header; launch restated from LAUNCH_SPEC_INC_ATTENTION_SCORE_KERNEL (:391-442): grid (num_q_heads,
+// speculative_request_num), shared memory sized for max_sequence_length + max_spec_tree_token_num.
+template <typename DT, int THREADS_PER_BLOCK, int Dh, int Dh_MAX, int THREADS_PER_KEY, int THREADS_PER_VALUE>
+#include REF_SPEC_KERNEL_INC
+
+template <int Dh>
+static int launch_spec_half(void const *qkv, void const *kc, void const *vc, void *out, float scale, int max_seq, int hidden,
+                            void *request_infos, void *beam_request_infos, void *causal_mask, void *request_completed,
+                            int num_q_heads, int num_spec_requests, cudaStream_t stream) {
+  constexpr int TPV = threads_per_value_t<half, Dh>::value;
+  size_t const smem = smem_size_in_bytes<half>(Dh, max_seq, TPV, 128);
+  auto kern = compute_spec_inc_attention_kernel_generation_kernel<half, 128, Dh, Dh, 4, TPV>;
+  if (smem > 48 * 1024) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  }
+  dim3 grid(num_q_heads, num_spec_requests);
+  kern<<<grid, 128, smem, stream>>>((half const *)qkv, (half const *)kc, (half const *)vc, (half *)out, scale, max_seq, Dh,
+                                    hidden, (BatchConfig::PerRequestInfo *)request_infos,
+                                    (BeamSearchBatchConfig::BeamSearchPerRequestInfo *)beam_request_infos,
+                                    (BatchConfig::BitMask *)causal_mask, (bool *)request_completed);
+  return (int)cudaGetLastError();
+}
+
 template <int Dh>
 static int launch_half(void const *qkv, void const *kc, void const *vc, void *out, float scale, int max_seq, int hidden,
                        void *request_infos, int num_q_heads, int num_gen_tokens, cudaStream_t stream) {
@@ -78,6 +102,27 @@ int ref_inc_generation_half(void const *qkv, void const *key_cache, void const *
   }
   return -1;
 }
+// max_seq = max_sequence_length + max_spec_tree_token_num (the cache's row count in beam mode); the four descriptor
+// arrays are device copies of BeamSearchBatchConfig::{requestsInfo, beamRequestsInfo, causalMask, request_completed}.
+int ref_spec_generation_half(void const *qkv, void const *key_cache, void const *value_cache, void *out, float scale,
+                             int max_seq, int head_dim, int hidden, void *request_infos_dev, void *beam_request_infos_dev,
+                             void *causal_mask_dev, void *request_completed_dev, int num_q_heads, int num_spec_requests,
+                             void *stream) {
+  using namespace FlexFlow::Kernels::IncMultiHeadAttention;
+  if (head_dim == 128) {
+    return launch_spec_half<128>(qkv, key_cache, value_cache, out, scale, max_seq, hidden, request_infos_dev,
+                                 beam_request_infos_dev, causal_mask_dev, request_completed_dev, num_q_heads,
+                                 num_spec_requests, (cudaStream_t)stream);
+  }
+  if (head_dim == 64) {
+    return launch_spec_half<64>(qkv, key_cache, value_cache, out, scale, max_seq, hidden, request_infos_dev,
+                                beam_request_infos_dev, causal_mask_dev, request_completed_dev, num_q_heads,
+                                num_spec_requests, (cudaStream_t)stream);
+  }
+  return -1;
+}
+int ref_sizeof_beam_per_request_info(void) { return (int)sizeof(FlexFlow::BeamSearchBatchConfig::BeamSearchPerRequestInfo); }
+int ref_sizeof_bit_mask(void) { return (int)sizeof(FlexFlow::BatchConfig::BitMask); }
 // compute_qkv_kernel's RoPE step (:838-857): in place on devQKVProjArray [tokens][3][hidden]; complex_scratch holds
 // tokens * hidden cuFloatComplex; token_infos_dev is a device copy of BatchConfig::tokensInfo.
 int ref_apply_rotary_embedding_half(void *qkv, void *complex_scratch, void const *token_infos_dev, float rope_theta,

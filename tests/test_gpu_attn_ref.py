@@ -108,3 +108,51 @@ def test_rope_kv_append_and_decode_against_the_reference_kernels(dh, nq, llama3)
     out_ref = _reference_decode(p, bc, rot, lens, max_requests, max_seq)
     assert TL.rel_err(got, out_ref) < 1e-2, TL.rel_err(got, out_ref)
     assert TL.rel_err(orc, out_ref) < 2e-3, TL.rel_err(orc, out_ref)
+
+
+@needs_ref
+@pytest.mark.parametrize("dh,nq", [(64, 12), (128, 8)])
+def test_spec_beam_attention_against_the_reference_kernel(dh, nq):
+    """SSM beam step (SpecIncMultiHeadSelfAttention): the reference's own
+    compute_spec_inc_attention_kernel_generation_kernel (spec_...cu:36-309) on the product's cache contents, tree shapes
+    (1, 1, 3) and (3, 1) as the reference builds them (spec_infer.cc:337-339)."""
+    import torch
+    from gpu_harness import Pair, make_qkv
+    ref = O.ref_attn_lib()
+    assert ref.ref_sizeof_beam_per_request_info() == C.sizeof(B.BeamSearchPerRequestInfo)
+    assert ref.ref_sizeof_bit_mask() == C.sizeof(B.BitMask)
+    rng = np.random.default_rng(dh + 7)
+    max_requests, max_seq = 6, 400
+    p = Pair(B.BEAM_SEARCH_MODE, "half", nq, nq, dh, max_requests, max_seq, 128, apply_rope=False, quirks=1)
+    spec = [dict(slot=0, non_tree=50, widths=[1, 1, 3]), dict(slot=3, non_tree=300, widths=[3, 1])]
+    p.fill_cache(rng, 0, 50 + 3)
+    p.fill_cache(rng, 3, 300 + 2)
+    bc = TL.make_beam_batch(spec)
+    T, H = bc.num_tokens, nq * dh
+    qkv = make_qkv(rng, T, nq, nq, dh, "half")
+    got, orc = p.forward_both(bc, qkv)
+    rows = max_seq + B.MAX_SPEC_TREE_TOKEN_NUM  # cache rows in beam mode (inc_...cu:1691-1716)
+    kc = torch.zeros(max_requests, rows, H, dtype=torch.float16, device="cuda")
+    vc = torch.zeros_like(kc)
+    for r in spec:
+        bm = bc.causalMask[r["slot"]]
+        n = bm.non_tree_cache_size + bm.tree_size + bm.prompt_size - 1  # totalCacheSize, spec_...cu:93-94
+        k, v = p.m.read_kv(r["slot"], 0, n)
+        kc[r["slot"], :n] = k.reshape(n, H)
+        vc[r["slot"], :n] = v.reshape(n, H)
+
+    def dev(x):
+        return torch.from_numpy(np.frombuffer(bytes(x), dtype=np.uint8).copy()).cuda()
+    ri, bri, cm, rc_ = dev(bc.requestsInfo), dev(bc.beamRequestsInfo), dev(bc.causalMask), dev(bc.request_completed)
+    qkv_dev = torch.from_numpy(np.ascontiguousarray(qkv, dtype=np.float32)).to("cuda", torch.float16).contiguous()
+    out = torch.full((T, H), float("nan"), dtype=torch.float16, device="cuda")
+    rc = ref.ref_spec_generation_half(C.c_void_p(qkv_dev.data_ptr()), C.c_void_p(kc.data_ptr()), C.c_void_p(vc.data_ptr()),
+                                      C.c_void_p(out.data_ptr()), 1.0 / np.sqrt(dh), rows, dh, H, C.c_void_p(ri.data_ptr()),
+                                      C.c_void_p(bri.data_ptr()), C.c_void_p(cm.data_ptr()), C.c_void_p(rc_.data_ptr()),
+                                      nq, bc.speculative_request_num, C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    torch.cuda.synchronize()
+    out = out.float().cpu().numpy()
+    assert np.isfinite(out).all()
+    assert TL.rel_err(got, out) < 1e-2, TL.rel_err(got, out)
+    assert TL.rel_err(orc, out) < 2e-3, TL.rel_err(orc, out)

@@ -1,1 +1,1 @@
-timeout 600 python -m pytest tests/test_gpu_norm_argmax.py -x -q -k "reference" --timeout 300 2>&1 | tail -12
+timeout 600 python -m pytest tests/test_gpu_attn_ref.py -x -q --timeout 300 2>&1 | tail -14
