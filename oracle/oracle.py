@@ -56,6 +56,9 @@ def ref_attn_lib():
                                                                         C.c_int, C.c_int, C.c_void_p]
         _ref_attn.ref_spec_generation_half.argtypes = [C.c_void_p] * 4 + [C.c_float, C.c_int, C.c_int, C.c_int] + \
             [C.c_void_p] * 4 + [C.c_int, C.c_int, C.c_void_p]
+        _ref_attn.ref_tree_verify_half.argtypes = [C.c_void_p] * 4 + [C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                                                     C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                                                     C.c_void_p]
         _ref_attn.ref_apply_rotary_embedding_half.argtypes = [C.c_void_p] * 3 + [C.c_float, C.c_int, C.c_float, C.c_float,
                                                                                  C.c_float, C.c_int, C.c_int, C.c_int,
                                                                                  C.c_int, C.c_void_p]

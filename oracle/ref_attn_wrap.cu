@@ -47,6 +47,37 @@ __global__ void
 template <typename DT, int THREADS_PER_BLOCK, int Dh, int Dh_MAX, int THREADS_PER_KEY, int THREADS_PER_VALUE>
 #include REF_SPEC_KERNEL_INC
 
+// compute_attention_kernel_fused_kernel (src/ops/tree_inc_multihead_self_attention.cu:35-333), same template header.
+// The launch restates LAUNCH_TREE_VERIFY_ATTENTION_SCORE_KERNEL (:494-573) and smem_size_in_bytes_tree
+// (inc_multihead_self_attention_utils.cuh:494-534; restated because the header's version calls
+// BatchConfig::max_requests_per_batch(), which lives in the runtime).  That size follows the QUERY length only (SURVEY
+// F7) while the kernel indexes its logits by key position, so the launcher refuses batches whose longest request
+// would write past the allocation: -2.
+template <typename DT, int THREADS_PER_BLOCK, int Dh, int Dh_MAX, int THREADS_PER_KEY, int THREADS_PER_VALUE>
+#include REF_TREE_KERNEL_INC
+
+template <int Dh>
+static int launch_tree_half(void const *qkv, void const *kc, void const *vc, void *out, float scale, int max_seq,
+                            int max_tokens, int hidden, void *request_infos, int num_q_heads, int num_requests,
+                            void *causal_mask, void *request_completed, int max_query_length, int max_total_length,
+                            cudaStream_t stream) {
+  constexpr int TPV = threads_per_value_t<half, Dh>::value;
+  size_t const qk_sz = div_up(max_query_length + 1, 4) * 16; // utils.cuh:515-518
+  size_t const softmax_sz = 2 * qk_sz;
+  size_t const q_size = Dh * sizeof(half);
+  size_t const red_sz = (128 / TPV) * Dh * sizeof(float) / 2;
+  size_t const total = softmax_sz + red_sz + q_size; // shared_mem[1], :531-533
+  if ((size_t)max_total_length * sizeof(float) > total) {
+    return -2;
+  }
+  dim3 grid(num_q_heads, num_requests);
+  compute_attention_kernel_fused_kernel<half, 128, Dh, Dh, 4, TPV><<<grid, 128, total, stream>>>(
+      (half const *)qkv, (half const *)kc, (half const *)vc, (half *)out, scale, max_seq, max_tokens, Dh, hidden,
+      (BatchConfig::PerRequestInfo *)request_infos, num_q_heads, num_requests, (BatchConfig::BitMask *)causal_mask,
+      (bool *)request_completed, (int)qk_sz);
+  return (int)cudaGetLastError();
+}
+
 template <int Dh>
 static int launch_spec_half(void const *qkv, void const *kc, void const *vc, void *out, float scale, int max_seq, int hidden,
                             void *request_infos, void *beam_request_infos, void *causal_mask, void *request_completed,
@@ -118,6 +149,25 @@ int ref_spec_generation_half(void const *qkv, void const *key_cache, void const 
     return launch_spec_half<64>(qkv, key_cache, value_cache, out, scale, max_seq, hidden, request_infos_dev,
                                 beam_request_infos_dev, causal_mask_dev, request_completed_dev, num_q_heads,
                                 num_spec_requests, (cudaStream_t)stream);
+  }
+  return -1;
+}
+// max_seq = max_sequence_length + max_spec_tree_token_num; max_query_length / max_total_length over the active requests
+// as smem_size_in_bytes_tree computes them (num_tokens_in_batch, first_token_depth_in_request + num_tokens_in_batch).
+int ref_tree_verify_half(void const *qkv, void const *key_cache, void const *value_cache, void *out, float scale,
+                         int max_seq, int max_tokens_per_batch, int head_dim, int hidden, void *request_infos_dev,
+                         int num_q_heads, int num_active_requests, void *causal_mask_dev, void *request_completed_dev,
+                         int max_query_length, int max_total_length, void *stream) {
+  using namespace FlexFlow::Kernels::IncMultiHeadAttention;
+  if (head_dim == 128) {
+    return launch_tree_half<128>(qkv, key_cache, value_cache, out, scale, max_seq, max_tokens_per_batch, hidden,
+                                 request_infos_dev, num_q_heads, num_active_requests, causal_mask_dev,
+                                 request_completed_dev, max_query_length, max_total_length, (cudaStream_t)stream);
+  }
+  if (head_dim == 64) {
+    return launch_tree_half<64>(qkv, key_cache, value_cache, out, scale, max_seq, max_tokens_per_batch, hidden,
+                                request_infos_dev, num_q_heads, num_active_requests, causal_mask_dev,
+                                request_completed_dev, max_query_length, max_total_length, (cudaStream_t)stream);
   }
   return -1;
 }

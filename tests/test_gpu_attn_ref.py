@@ -156,3 +156,59 @@ def test_spec_beam_attention_against_the_reference_kernel(dh, nq):
     assert np.isfinite(out).all()
     assert TL.rel_err(got, out) < 1e-2, TL.rel_err(got, out)
     assert TL.rel_err(orc, out) < 2e-3, TL.rel_err(orc, out)
+
+
+def _reference_tree_verify(p, bc, qkv_dev, reqs, max_requests, rows, max_tokens):
+    import torch
+    ref = O.ref_attn_lib()
+    H, T = p.H, bc.num_tokens
+    kc = torch.zeros(max_requests, rows, H, dtype=torch.float16, device="cuda")
+    vc = torch.zeros_like(kc)
+    max_q = max_total = 0
+    for r in reqs:
+        n = r["committed_len"] + len(r["parent"])
+        k, v = p.m.read_kv(r["slot"], 0, n)  # committed rows + the tree rows this step appended
+        kc[r["slot"], :n] = k.reshape(n, H)
+        vc[r["slot"], :n] = v.reshape(n, H)
+        max_q, max_total = max(max_q, len(r["parent"])), max(max_total, n)
+
+    def dev(x):
+        return torch.from_numpy(np.frombuffer(bytes(x), dtype=np.uint8).copy()).cuda()
+    ri, cm, rc_ = dev(bc.requestsInfo), dev(bc.causalMask), dev(bc.request_completed)
+    out = torch.full((T, H), float("nan"), dtype=torch.float16, device="cuda")
+    rc = ref.ref_tree_verify_half(C.c_void_p(qkv_dev.data_ptr()), C.c_void_p(kc.data_ptr()), C.c_void_p(vc.data_ptr()),
+                                  C.c_void_p(out.data_ptr()), 1.0 / np.sqrt(p.dh), rows, max_tokens, p.dh, H,
+                                  C.c_void_p(ri.data_ptr()), p.nq, len(reqs), C.c_void_p(cm.data_ptr()),
+                                  C.c_void_p(rc_.data_ptr()), max_q, max_total,
+                                  C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0, rc  # -2: the batch would overrun the reference kernel's shared memory (F7) and is not launched
+    torch.cuda.synchronize()
+    return out.float().cpu().numpy()
+
+
+@needs_ref
+@pytest.mark.parametrize("dh,nq", [(128, 8), (64, 12)])
+def test_tree_verify_attention_against_the_reference_kernel(dh, nq):
+    """TreeIncMultiHeadSelfAttention: the reference's own compute_attention_kernel_fused_kernel (tree_...cu:35-333) on
+    the product's cache contents.  Trees of at most 25 nodes (the reference's `1 << qi` mask shift, F6) and contexts
+    short enough for its query-length-sized shared memory (F7: the launcher refuses anything longer); the reference
+    carries qk_max across the query tokens of a request, which only moves the softmax's reference point."""
+    import torch
+    from gpu_harness import Pair, make_qkv
+    rng = np.random.default_rng(dh + 11)
+    max_requests, max_seq, max_tokens = 8, 1024, 128
+    p = Pair(B.TREE_VERIFY_MODE, "half", nq, nq, dh, max_requests, max_seq, max_tokens, apply_rope=False, quirks=1)
+    reqs = [dict(slot=0, committed_len=40, parent=TL.tree_from_widths([1, 1, 3])),
+            dict(slot=2, committed_len=300, parent=TL.random_tree(rng, 25)),
+            dict(slot=5, committed_len=550, parent=TL.random_tree(rng, 25)),
+            dict(slot=6, committed_len=7, parent=[-1])]
+    for r in reqs:
+        p.fill_cache(rng, r["slot"], r["committed_len"])
+    bc = TL.make_tree_batch(reqs)
+    qkv = make_qkv(rng, bc.num_tokens, nq, nq, dh, "half")
+    got, orc = p.forward_both(bc, qkv)
+    qkv_dev = torch.from_numpy(np.ascontiguousarray(qkv, dtype=np.float32)).to("cuda", torch.float16).contiguous()
+    ref = _reference_tree_verify(p, bc, qkv_dev, reqs, max_requests, max_seq + B.MAX_SPEC_TREE_TOKEN_NUM, max_tokens)
+    assert np.isfinite(ref).all()
+    assert TL.rel_err(got, ref) < 1e-2, TL.rel_err(got, ref)
+    assert TL.rel_err(orc, ref) < 2e-3, TL.rel_err(orc, ref)
