@@ -104,6 +104,47 @@ def reference_decode_kernel_ms(nq=32, dh=128, nreq=16, ctx=2048, layers=4, iters
     return e0.elapsed_time(e1) / (iters * layers)
 
 
+def reference_tree_kernel_ms(rng, nq=32, dh=128, nreq=8, ctx=512, ntree=25, layers=4, iters=10):
+    """The reference's own tree-verify kernel (oracle/_ref/libref_attn.so) at 7B shapes with the largest trees the
+    reference builds (25 nodes) and the longest context its shared-memory sizing survives: ctx 512."""
+    import ctypes as C
+    from oracle import oracle as O
+    ref = O.ref_attn_lib()
+    if ref is None:
+        return None
+    H, rows = nq * dh, 1024 + B.MAX_SPEC_TREE_TOKEN_NUM
+    g = torch.Generator(device="cuda").manual_seed(2)
+    caches = [(torch.randn(nreq, rows, H, generator=g, device="cuda", dtype=torch.float16),
+               torch.randn(nreq, rows, H, generator=g, device="cuda", dtype=torch.float16)) for _ in range(layers)]
+    bc = TL.make_tree_batch([dict(slot=s, committed_len=ctx, parent=TL.random_tree(rng, ntree)) for s in range(nreq)])
+
+    def dev(x):
+        return torch.from_numpy(np.frombuffer(bytes(x), dtype=np.uint8).copy()).cuda()
+    ri, cm, rc_ = dev(bc.requestsInfo), dev(bc.causalMask), dev(bc.request_completed)
+    T = bc.num_tokens
+    qkv = torch.randn(T, 3, H, generator=g, device="cuda", dtype=torch.float16)
+    out = torch.empty(T, H, device="cuda", dtype=torch.float16)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def launch(kc, vc):
+        rc = ref.ref_tree_verify_half(C.c_void_p(qkv.data_ptr()), C.c_void_p(kc.data_ptr()), C.c_void_p(vc.data_ptr()),
+                                      C.c_void_p(out.data_ptr()), 1.0 / np.sqrt(dh), rows, 1024, dh, H, C.c_void_p(ri.data_ptr()),
+                                      nq, nreq, C.c_void_p(cm.data_ptr()), C.c_void_p(rc_.data_ptr()), ntree, ctx + ntree, st)
+        assert rc == 0, rc
+    for kc, vc in caches:
+        launch(kc, vc)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda._sleep(2_000_000)
+    e0.record()
+    for _ in range(iters):
+        for kc, vc in caches:
+            launch(kc, vc)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / (iters * layers)
+
+
 def main():
     rng = np.random.default_rng(0)
     res = []
@@ -112,7 +153,7 @@ def main():
     def decode7b():
         lens = {s: 2047 for s in range(16)}
         return TL.make_inc_batch([dict(slot=s, first_depth=2047, ntok=1) for s in range(16)]), lens
-    if only not in ("cfg4", "cfg5"):
+    if only not in ("cfg4", "cfg5", "treeref"):
         res.append(run("cfg2 7B decode b16 ctx2048", B.INC_DECODING_MODE, 32, 32, 128, decode7b, 16, 2048, 16))
         ref_ms = reference_decode_kernel_ms()
         if ref_ms is not None:
@@ -130,9 +171,21 @@ def main():
         return f
     if only != "cfg4" or True:
         pass
-    if only != "cfg5":
+    if only not in ("cfg5", "treeref"):
         res.append(run("cfg4 7B tree-verify b8 x64 ctx1024", B.TREE_VERIFY_MODE, 32, 32, 128, tree7b(64), 8, int(os.environ.get("FFB_BENCH_CTX", "1024")) + 76, 512))
     if only == "cfg4":
+        return
+    if only in (None, "treeref"):
+        def tree_short():
+            lens = {s: 512 for s in range(8)}
+            return TL.make_tree_batch([dict(slot=s, committed_len=512, parent=TL.random_tree(rng, 25)) for s in range(8)]), lens
+        res.append(run("7B tree-verify b8 x25 ctx512 (largest case the reference kernel can run)", B.TREE_VERIFY_MODE, 32, 32, 128, tree_short, 8, 1024, 512))
+        ref_ms = reference_tree_kernel_ms(rng)
+        if ref_ms is not None:
+            res[-1]["reference_kernel_ms"] = ref_ms
+            res[-1]["speedup_vs_reference_kernel"] = ref_ms / res[-1]["kernel_ms"]
+            print("reference tree-verify kernel (compiled from the reference tree, same GPU): %.1f us -> x%.2f" % (ref_ms * 1e3, ref_ms / res[-1]["kernel_ms"]), flush=True)
+    if only == "treeref":
         return
     if only != "cfg5":
         res.append(run("cfg4' 7B tree-verify b8 x25 ctx1024 (reference max tree)", B.TREE_VERIFY_MODE, 32, 32, 128, tree7b(25), 8, 1100, 512))
