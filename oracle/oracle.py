@@ -59,6 +59,8 @@ def ref_attn_lib():
         _ref_attn.ref_tree_verify_half.argtypes = [C.c_void_p] * 4 + [C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                                                      C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                                                      C.c_void_p]
+        _ref_attn.ref_commit_tokens_half.argtypes = [C.c_void_p] * 4 + [C.c_int] * 5 + [C.c_void_p]
+        _ref_attn.ref_update_tree_branch_kv_cache_half.argtypes = [C.c_void_p] * 5 + [C.c_int] * 4 + [C.c_void_p]
         _ref_attn.ref_apply_rotary_embedding_half.argtypes = [C.c_void_p] * 3 + [C.c_float, C.c_int, C.c_float, C.c_float,
                                                                                  C.c_float, C.c_int, C.c_int, C.c_int,
                                                                                  C.c_int, C.c_void_p]

@@ -56,6 +56,14 @@ template <typename DT, int THREADS_PER_BLOCK, int Dh, int Dh_MAX, int THREADS_PE
 template <typename DT, int THREADS_PER_BLOCK, int Dh, int Dh_MAX, int THREADS_PER_KEY, int THREADS_PER_VALUE>
 #include REF_TREE_KERNEL_INC
 
+// commit_tokens_kernel (tree_...cu:335-372) and update_tree_branch_kv_cache_fused (:433-478): the tree-mode KV
+// placement; `template <typename DT>` supplied here, launches restated from commit_tokens (:374-398, with the
+// reference's parallelism of hidden * KV_WEIGHT_NUM * tokens) and compute_attention_kernel_fused (:536-555).
+template <typename DT>
+#include REF_COMMIT_KERNEL_INC
+template <typename DT>
+#include REF_UPDATE_KERNEL_INC
+
 template <int Dh>
 static int launch_tree_half(void const *qkv, void const *kc, void const *vc, void *out, float scale, int max_seq,
                             int max_tokens, int hidden, void *request_infos, int num_q_heads, int num_requests,
@@ -171,6 +179,36 @@ int ref_tree_verify_half(void const *qkv, void const *key_cache, void const *val
   }
   return -1;
 }
+// prev_qkv: devQKVProjArray of the PREVIOUS verify batch; committed_dev: device copy of committed_tokens[].
+int ref_commit_tokens_half(void const *prev_qkv, void *key_cache, void *value_cache, void const *committed_dev, int proj,
+                           int num_tokens_to_commit, int num_active_tokens_in_last_batch, int max_seq, int hidden,
+                           void *stream) {
+  using namespace FlexFlow;
+  if (num_tokens_to_commit <= 0) {
+    return 0;
+  }
+  int const parallelism = hidden * 2 * num_tokens_to_commit;
+  int blocks = (parallelism + 1023) / 1024;
+  blocks = blocks > 32768 ? 32768 : blocks;
+  Kernels::IncMultiHeadAttention::commit_tokens_kernel<half><<<blocks, parallelism < 1024 ? parallelism : 1024, 0, (cudaStream_t)stream>>>(
+      (half const *)prev_qkv, (half *)key_cache, (half *)value_cache,
+      (TreeVerifyBatchConfig::CommittedTokensInfo const *)committed_dev, proj, proj, proj, num_tokens_to_commit,
+      num_active_tokens_in_last_batch, max_seq, hidden);
+  return (int)cudaGetLastError();
+}
+int ref_update_tree_branch_kv_cache_half(void const *qkv, void *key_cache, void *value_cache, void const *token_infos_dev,
+                                         void *request_infos_dev, int proj, int num_new_tokens, int max_seq, int hidden,
+                                         void *stream) {
+  using namespace FlexFlow;
+  int const parallelism = hidden * num_new_tokens;
+  int blocks = (parallelism + 1023) / 1024;
+  blocks = blocks > 32768 ? 32768 : blocks;
+  Kernels::IncMultiHeadAttention::update_tree_branch_kv_cache_fused<half><<<blocks, parallelism < 1024 ? parallelism : 1024, 0, (cudaStream_t)stream>>>(
+      (half const *)qkv, (half *)key_cache, (half *)value_cache, (TreeVerifyBatchConfig::PerTokenInfo const *)token_infos_dev,
+      (BatchConfig::PerRequestInfo *)request_infos_dev, proj, proj, proj, num_new_tokens, max_seq, hidden);
+  return (int)cudaGetLastError();
+}
+int ref_sizeof_committed_tokens_info(void) { return (int)sizeof(FlexFlow::TreeVerifyBatchConfig::CommittedTokensInfo); }
 int ref_sizeof_beam_per_request_info(void) { return (int)sizeof(FlexFlow::BeamSearchBatchConfig::BeamSearchPerRequestInfo); }
 int ref_sizeof_bit_mask(void) { return (int)sizeof(FlexFlow::BatchConfig::BitMask); }
 // compute_qkv_kernel's RoPE step (:838-857): in place on devQKVProjArray [tokens][3][hidden]; complex_scratch holds

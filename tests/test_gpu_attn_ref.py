@@ -212,3 +212,64 @@ def test_tree_verify_attention_against_the_reference_kernel(dh, nq):
     assert np.isfinite(ref).all()
     assert TL.rel_err(got, ref) < 1e-2, TL.rel_err(got, ref)
     assert TL.rel_err(orc, ref) < 2e-3, TL.rel_err(orc, ref)
+
+
+@needs_ref
+def test_tree_kv_placement_and_commit_against_the_reference_kernels():
+    """Two verify steps with a commit in between: the reference's own update_tree_branch_kv_cache_fused
+    (tree_...cu:433-478) and commit_tokens_kernel (:335-372) run on a mirror of the cache in the reference layout; after
+    each step every cache row of every request equals the product's, bit for bit (RoPE off: the rows are copies)."""
+    import torch
+    from gpu_harness import Pair, make_qkv
+    ref = O.ref_attn_lib()
+    assert ref.ref_sizeof_committed_tokens_info() == C.sizeof(B.CommittedTokensInfo)
+    rng = np.random.default_rng(23)
+    nq, dh, max_requests, max_seq, max_tokens = 8, 64, 6, 256, 128
+    H, rows = nq * dh, max_seq + B.MAX_SPEC_TREE_TOKEN_NUM
+    p = Pair(B.TREE_VERIFY_MODE, "half", nq, nq, dh, max_requests, max_seq, max_tokens, apply_rope=False, quirks=1)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    kc = torch.zeros(max_requests, rows, H, dtype=torch.float16, device="cuda")
+    vc = torch.zeros_like(kc)
+    for slot, n in ((1, 100), (4, 33)):
+        p.fill_cache(rng, slot, n)
+        k, v = p.m.read_kv(slot, 0, n)
+        kc[slot, :n], vc[slot, :n] = k.reshape(n, H), v.reshape(n, H)
+
+    def dev(x):
+        return torch.from_numpy(np.frombuffer(bytes(x), dtype=np.uint8).copy()).cuda()
+
+    def check(lens):
+        for slot, n in lens.items():
+            k, v = p.m.read_kv(slot, 0, n)
+            torch.cuda.synchronize()
+            assert torch.equal(k.reshape(n, H), kc[slot, :n]), slot
+            assert torch.equal(v.reshape(n, H), vc[slot, :n]), slot
+
+    def ref_update(bc, qkv_dev):
+        ti, ri = dev(bc.tokensInfo), dev(bc.requestsInfo)
+        assert ref.ref_update_tree_branch_kv_cache_half(C.c_void_p(qkv_dev.data_ptr()), C.c_void_p(kc.data_ptr()),
+                                                        C.c_void_p(vc.data_ptr()), C.c_void_p(ti.data_ptr()),
+                                                        C.c_void_p(ri.data_ptr()), dh, bc.num_tokens, rows, H, st) == 0
+        torch.cuda.synchronize()
+
+    par_a, par_b = TL.tree_from_widths([1, 1, 3]), TL.random_tree(rng, 12)
+    bc1 = TL.make_tree_batch([dict(slot=1, committed_len=100, parent=par_a), dict(slot=4, committed_len=33, parent=par_b)])
+    qkv1 = make_qkv(rng, bc1.num_tokens, nq, nq, dh, "half")
+    p.gpu_forward(bc1, qkv1)
+    q1 = torch.from_numpy(np.ascontiguousarray(qkv1, dtype=np.float32)).to("cuda", torch.float16).contiguous()
+    ref_update(bc1, q1)
+    check({1: 100 + len(par_a), 4: 33 + len(par_b)})
+    # accept root + two nodes of request 1 (batch idx 0, 1, 2) and root + node 1 of request 4 (idx 6, 7); commit them
+    off4 = len(par_a)
+    commits = [(0, 1, 100), (1, 1, 101), (2, 1, 102), (off4, 4, 33), (off4 + 1, 4, 34)]
+    par_c = TL.tree_from_widths([2, 2])
+    bc2 = TL.make_tree_batch([dict(slot=1, committed_len=103, parent=par_c), dict(slot=4, committed_len=35, parent=par_c)],
+                             commits=commits)
+    qkv2 = make_qkv(rng, bc2.num_tokens, nq, nq, dh, "half")
+    p.gpu_forward(bc2, qkv2)
+    cm = dev(bc2.committed_tokens)
+    assert ref.ref_commit_tokens_half(C.c_void_p(q1.data_ptr()), C.c_void_p(kc.data_ptr()), C.c_void_p(vc.data_ptr()),
+                                      C.c_void_p(cm.data_ptr()), dh, bc2.num_tokens_to_commit, bc1.num_tokens, rows, H, st) == 0
+    q2 = torch.from_numpy(np.ascontiguousarray(qkv2, dtype=np.float32)).to("cuda", torch.float16).contiguous()
+    ref_update(bc2, q2)
+    check({1: 103 + len(par_c), 4: 35 + len(par_c)})

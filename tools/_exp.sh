@@ -1,2 +1,1 @@
-timeout 300 python tools/bench_attn.py --only treeref 2>&1 | tail -3
-timeout 400 python tools/bench_attn.py --json gpurun_out/bench_attn.json 2>&1 | grep -c case
+timeout 600 python -m pytest tests/test_gpu_attn_ref.py -x -q --timeout 300 2>&1 | tail -14
