@@ -300,6 +300,10 @@ def run_ours(args):
             line["tree_verify"] = {"error": repr(e)}
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
+            try:
+                line["reference_gpu_kernels"] = reference_gpu_kernels(k_ms)
+            except Exception as e:  # the headline line must still print
+                line["reference_gpu_kernels"] = {"error": repr(e)}
             line["cpu_baseline"] = cpu_baseline(max_seconds=25.0)
         print(json.dumps(line))
     if world > 1:
@@ -387,6 +391,32 @@ def quantized_extra(args, dev, model, step, ms_fp16):
         for l, (m, w) in zip(lins, saved):
             l.meta, l.weight = m, w
     return res
+
+
+def reference_gpu_kernels(ours_decode_ms):
+    """north_star: "the reference's own FlexFlow GPU build is timed too, where it compiles for this box".  The whole
+    build needs Legion; what compiles from the reference tree on its own - the decode and tree-verify attention
+    kernels - is built into oracle/_ref/ (oracle/Makefile target `ref`, in the container that mounts /root/reference)
+    and timed here on the same GPU at the same shapes.  A reported baseline beside cpu_baseline, not the product."""
+    import numpy as np
+    root = os.path.dirname(os.path.abspath(__file__))
+    for p in (root, os.path.join(root, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    from tools import bench_attn as BA
+    dec = BA.reference_decode_kernel_ms()
+    if dec is None:
+        return {"unavailable": "oracle/_ref/libref_attn.so not built (make -C oracle ref needs /root/reference)"}
+    tree = BA.reference_tree_kernel_ms(np.random.default_rng(0))
+    return {"kind": "reference kernels compiled for sm_100a from the reference tree (oracle/_ref), same GPU",
+            "decode_attn": {"workload": "configs[1] shapes: 16 requests x 2048 context, 32 heads x 128, per layer",
+                            "reference_kernel_us": dec * 1e3, "ours_us": ours_decode_ms * 1e3,
+                            "speedup": dec / ours_decode_ms},
+            "tree_verify_attn": {"workload": "8 requests x 25 tree tokens x 512 context (the largest case the reference "
+                                             "kernel's shared-memory sizing allows), 32 heads x 128, per layer",
+                                 "reference_kernel_us": tree * 1e3,
+                                 "note": "ours on the same inputs: tools/bench_attn.py --only treeref "
+                                         "(profiles/r01_bench_attn.json)"}}
 
 
 def block_ops_extra(dev):
