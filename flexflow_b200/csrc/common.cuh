@@ -88,6 +88,12 @@ __device__ __forceinline__ uint4 ldg_stream(void const *p) {
   return r;
 }
 
+__device__ __forceinline__ uint2 ldg_stream64(void const *p) {
+  uint2 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+  return r;
+}
+
 // ---- per-query descriptor written by the prep kernel, consumed by the attention kernels ----
 // A query attends keys [0, kv_len) of request slot `slot`; keys >= ntcs are additionally gated by
 // bit `bit` of causalMask[slot].mask[key - ntcs] when bit >= 0 (tree / beam modes).

@@ -46,8 +46,13 @@ template <typename T> __device__ __forceinline__ uint32_t pack2(T a, T b) {
 constexpr int LS_WARPS = 8;
 // Decode (MT == 1) occupancy, measured on the 7B qkv_proj blob (384 CTAs): int8 with one chunk in flight per warp and
 // 3 CTAs per SM (80 registers: every CTA resident in one wave) 23 us, against 35 us with two chunks and 2 CTAs per SM
-// (1.3 waves, ncu: long-scoreboard stalls); int4 needs its 128 registers (39 us at 3 CTAs per SM, 26 us at 2).
-template <int QB> struct LsOcc { static constexpr int BLOCKS = QB == 8 ? 3 : 2; };
+// (1.3 waves, ncu: long-scoreboard stalls); int4 with 16-byte chunks needs 128 registers (39 us at 3 CTAs per SM, 26.5 us
+// at 2), so its decode variant takes 8-byte chunks (int8's register profile, 3 CTAs per SM): 25.4 us - the same time as
+// int8 for half the bytes, i.e. both are bound by the per-element instructions of the bit-exact rule, not by HBM.
+#ifndef LS_INT4_KE16
+#define LS_INT4_KE16 1
+#endif
+template <int QB> struct LsOcc { static constexpr int BLOCKS = (QB == 8 || (QB == 4 && LS_INT4_KE16)) ? 3 : 2; };
 
 // QB: 0 = DT weights, 8 = int8 blob, 4 = int4 blob.  The k -> mma-slot assignment is a fixed
 // permutation applied identically to A and B (a dot product is order-free), chosen so every lane
@@ -56,7 +61,9 @@ template <typename T, int QB, int NT, int MT>
 __global__ void __launch_bounds__(LS_WARPS * 32, MT == 1 ? LsOcc<QB>::BLOCKS : 1)
 linear_stream_kernel(T const *__restrict__ A, uint8_t const *__restrict__ W, T const *__restrict__ bias,
                      T *__restrict__ out, int M, int K, int N) {
-  constexpr int KE = QB == 0 ? 8 : (QB == 8 ? 16 : 32); // k elements per lane per chunk (16 B of weights)
+  // k elements per lane per chunk: 16 B of weights, except int4 decode (MT == 1), which takes 8 B (16 nibbles) so that
+  // its register profile is int8's and 3 CTAs fit an SM
+  constexpr int KE = QB == 0 ? 8 : (QB == 8 ? 16 : ((MT == 1 && LS_INT4_KE16) ? 16 : 32));
   constexpr int KC = 4 * KE;                            // k elements per warp chunk
   constexpr int STEPS = KE / 4;                         // mma k-steps per chunk
   constexpr int AP = KE / 8;                            // 16-byte activation pieces per row per chunk
@@ -95,7 +102,12 @@ linear_stream_kernel(T const *__restrict__ A, uint8_t const *__restrict__ W, T c
 #pragma unroll
         for (int nt = 0; nt < NT; nt++) {
           size_t const e = (size_t)(n0 + nt * 8 + g) * K + k;
-          w[u][nt] = ldg_stream(QB == 0 ? W + e * 2 : (QB == 8 ? W + e : W + e / 2));
+          if (QB == 4 && KE == 16) {
+            uint2 const v = ldg_stream64(W + e / 2);
+            w[u][nt] = make_uint4(v.x, v.y, 0, 0);
+          } else {
+            w[u][nt] = ldg_stream(QB == 0 ? W + e * 2 : (QB == 8 ? W + e : W + e / 2));
+          }
         }
         if (QB != 0) {
 #pragma unroll
