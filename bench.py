@@ -464,6 +464,12 @@ def block_ops_extra(dev):
         am = ops.ArgMaxMeta(None)
         ms = timed(lambda i: ops.ArgMax.forward_kernel_wrapper(am, None, x[i], idx, None, rows), nbuf)
         alg = rows * vocab * 2 + rows * 4
+        if rows == BATCH:  # the SSM's token selection in beam mode: top 3 of each row
+            tk = ops.ArgTopKMeta(None, 3, speculative_decoding=True)
+            tidx = torch.empty(rows, 3, dtype=torch.int32, device=dev)
+            tval = torch.empty(rows, 3, dtype=torch.float32, device=dev)
+            ms3 = timed(lambda i: ops.ArgTopK.forward_kernel_wrapper(tk, None, x[i], tval, tidx, rows), nbuf)
+            res["arg_topk3_%dx%d" % (rows, vocab)] = {"us": ms3 * 1e3}
         res["argmax_%dx%d" % (rows, vocab)] = {"us": ms * 1e3, "algorithmic_bytes": alg,
                                                "gbs": alg / (ms * 1e-3) / 1e9,
                                                "frac_of_hbm_peak": alg / (ms * 1e-3) / 1e9 / peak}

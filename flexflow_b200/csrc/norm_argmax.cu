@@ -200,6 +200,85 @@ argmax_kernel(T const *__restrict__ in, int *__restrict__ indices, float *__rest
   }
 }
 
+// ArgTopK (src/ops/arg_topk.cu:340-449, the TensorFlow heap kernel launched with k threads per row): the k largest
+// entries of each row, best first, equal values in increasing index order.  One CTA per row; round r finds the maximum
+// among the entries that come strictly after round r-1's winner in that (value desc, index asc) order, so the result
+// is the reference's for any input, ties included.  k <= 16 (the reference's beam widths are <= 3).
+template <typename T>
+__global__ void __launch_bounds__(1024)
+arg_topk_kernel(T const *__restrict__ in, float *__restrict__ values, int *__restrict__ indices, int V, int k) {
+  int const row = blockIdx.x, tid = threadIdx.x, nthr = blockDim.x;
+  T const *p = in + (size_t)row * V;
+  int const nvec = ((size_t)row * V) % 8 == 0 ? V / 8 : 0;
+  __shared__ float sv[32];
+  __shared__ int si[32];
+  __shared__ float s_pv;
+  __shared__ int s_pi;
+  float pv = INFINITY; // previous winner: nothing precedes the first round
+  int pi = -1;
+  for (int r = 0; r < k; r++) {
+    float best = -INFINITY;
+    int bi = INT_MAX;
+    auto consider = [&](float v, int i) {
+      bool const eligible = v < pv || (v == pv && i > pi);
+      if (eligible && (v > best || (v == best && i < bi))) {
+        best = v;
+        bi = i;
+      }
+    };
+    for (int c = tid; c < nvec; c += nthr) {
+      float f[8];
+      unpack8<T>(__ldg(reinterpret_cast<uint4 const *>(p + (size_t)c * 8)), f); // rows are re-read k times: keep them in L1
+#pragma unroll
+      for (int e = 0; e < 8; e++) {
+        consider(f[e], c * 8 + e);
+      }
+    }
+    for (int i = nvec * 8 + tid; i < V; i += nthr) {
+      consider(DT<T>::to_f(p[i]), i);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      float const ov = __shfl_xor_sync(0xffffffffu, best, o);
+      int const oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ov > best || (ov == best && oi < bi)) {
+        best = ov;
+        bi = oi;
+      }
+    }
+    if ((tid & 31) == 0) {
+      sv[tid >> 5] = best;
+      si[tid >> 5] = bi;
+    }
+    __syncthreads();
+    if (tid < 32) {
+      int const nw = (nthr + 31) >> 5;
+      best = tid < nw ? sv[tid] : -INFINITY;
+      bi = tid < nw ? si[tid] : INT_MAX;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        float const ov = __shfl_xor_sync(0xffffffffu, best, o);
+        int const oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > best || (ov == best && oi < bi)) {
+          best = ov;
+          bi = oi;
+        }
+      }
+      if (tid == 0) {
+        s_pv = best;
+        s_pi = bi;
+        indices[(size_t)row * k + r] = bi == INT_MAX ? 0 : bi;
+        if (values != nullptr) {
+          values[(size_t)row * k + r] = best;
+        }
+      }
+    }
+    __syncthreads();
+    pv = s_pv;
+    pi = s_pi;
+  }
+}
+
 template <typename T>
 int launch_rms_norm(void const *x1, void const *x2, void const *w, void *res, void *out, int T_rows, int N, float eps,
                     cudaStream_t s) {
@@ -266,6 +345,31 @@ int ffb_argmax(void const *input_dev, int *indices_dev, float *prob_dev, int *pa
   } else {
     argmax_kernel<__nv_bfloat16><<<num_tokens, threads, 0, (cudaStream_t)stream>>>(
         (__nv_bfloat16 const *)input_dev, indices_dev, prob_dev, parent_dev, length);
+  }
+  FFB_LAUNCH_CHECK();
+  return FFB_OK;
+}
+
+int ffb_arg_topk(void const *input_dev, float *values_dev, int *indices_dev, int num_tokens, int length, int k,
+                 int dtype, ffb_stream_t stream) {
+  using namespace ffb;
+  if (int rc = ffb_check_device()) {
+    return rc;
+  }
+  FFB_REQUIRE(input_dev && indices_dev, "null argument");
+  FFB_REQUIRE(dtype == FFB_DT_HALF || dtype == FFB_DT_BF16, "dtype %d not supported", dtype);
+  FFB_REQUIRE(num_tokens >= 0 && length > 0 && k >= 1 && k <= 16 && k <= length, "bad shape %d x %d, k = %d", num_tokens,
+              length, k);
+  if (num_tokens == 0) {
+    return FFB_OK;
+  }
+  int const threads = length >= 8192 ? 1024 : 256;
+  if (dtype == FFB_DT_HALF) {
+    arg_topk_kernel<__half><<<num_tokens, threads, 0, (cudaStream_t)stream>>>((__half const *)input_dev, values_dev,
+                                                                              indices_dev, length, k);
+  } else {
+    arg_topk_kernel<__nv_bfloat16><<<num_tokens, threads, 0, (cudaStream_t)stream>>>((__nv_bfloat16 const *)input_dev,
+                                                                                     values_dev, indices_dev, length, k);
   }
   FFB_LAUNCH_CHECK();
   return FFB_OK;

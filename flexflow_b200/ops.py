@@ -335,3 +335,23 @@ class ArgMax:
         L.check(L.load().ffb_argmax(_ptr(input), _ptr(indices), _ptr(probs), _ptr(parent) if m.beam_search else
                                     C.c_void_p(0), batch_size, length, _dt_of(input), _stream()), "ffb_argmax")
         return probs
+
+
+class ArgTopKMeta:
+    """ArgTopKMeta (include/flexflow/ops/arg_topk.h): k, sorted (always best first here), speculative_decoding selects
+    the values output."""
+
+    def __init__(self, handler, k, speculative_decoding=False):
+        self.handle, self.k, self.speculative_decoding = handler, int(k), bool(speculative_decoding)
+
+
+class ArgTopK:
+    @staticmethod
+    def forward_kernel_wrapper(m, bc, input, probs, indices, batch_size):
+        """ArgTopK::forward_kernel_wrapper (src/ops/arg_topk.cu:451-541): input [batch_size][length] DT, indices int32
+        [batch_size][k], probs float32 [batch_size][k] (written in the speculative-decoding case)."""
+        length = input.numel() // batch_size
+        if indices.dtype != torch.int32:
+            raise L.FFBError("indices must be int32")
+        L.check(L.load().ffb_arg_topk(_ptr(input), _ptr(probs) if m.speculative_decoding else C.c_void_p(0), _ptr(indices),
+                                      batch_size, length, m.k, _dt_of(input), _stream()), "ffb_arg_topk")

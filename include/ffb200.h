@@ -201,6 +201,12 @@ int ffb_residual_rms_norm(void const *input1_dev, void const *input2_dev, void c
                           ffb_stream_t stream);
 int ffb_argmax(void const *input_dev, int *indices_dev, float *prob_dev, int *parent_dev, int num_tokens, int length,
                int dtype, ffb_stream_t stream);
+/* ArgTopK::forward_kernel (src/ops/arg_topk.cu:373-449; the SSM's token selection in beam mode,
+ * inference/models/llama.cc:277-295): indices[t][0..k) = the k largest entries of input[t][0..length), best first,
+ * equal values in increasing index order; values_dev (speculative decoding: the entries as float) may be NULL.
+ * The reference leaves values[t][k-1] unwritten (:330-331); here all k are written.  1 <= k <= 16. */
+int ffb_arg_topk(void const *input_dev, float *values_dev, int *indices_dev, int num_tokens, int length, int k,
+                 int dtype, ffb_stream_t stream);
 
 /* ---- host-side SpecInfer tree logic (integer only; runs on the host, no CUDA call) ---------------------------------
  * The bit masks these build are what ffb_tree_attn_forward / ffb_spec_attn_forward read from causalMask[], and

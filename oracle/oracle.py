@@ -78,6 +78,7 @@ def ref_norm_lib():
         _ref_norm = C.CDLL(_REF_NORM_SO)
         _ref_norm.ref_residual_rms_norm_half.argtypes = [C.c_void_p] * 7 + [C.c_int, C.c_int, C.c_float, C.c_void_p]
         _ref_norm.ref_rms_norm_half.argtypes = [C.c_void_p] * 5 + [C.c_int, C.c_int, C.c_float, C.c_void_p]
+        _ref_norm.ref_arg_topk_half.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
         _ref_norm.ref_argmax_half.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                               C.c_size_t, C.POINTER(C.c_size_t), C.c_void_p, C.c_void_p]
     return _ref_norm
@@ -113,6 +114,7 @@ def lib():
         _lib.orc_append_bitmask.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int]
         _lib.orc_residual_rms_norm.argtypes = [C.c_void_p] * 5 + [C.c_int, C.c_int, C.c_float, C.c_int]
         _lib.orc_argmax.argtypes = [C.c_void_p] * 4 + [C.c_int, C.c_int]
+        _lib.orc_arg_topk.argtypes = [C.c_void_p] * 3 + [C.c_int, C.c_int, C.c_int]
         _lib.orc_traverse_verify_tree.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 9
     return _lib
 
@@ -256,6 +258,17 @@ def argmax(x, beam_search=False):
     lib().orc_argmax(_p(x), _p(idx), _p(prob) if beam_search else None, _p(parent) if beam_search else None, rows,
                      length)
     return idx, prob, parent
+
+
+def arg_topk(x, k):
+    """x: [rows][length] float32.  Returns (indices [rows][k], values [rows][k] with the reference's unwritten last
+    column set to NaN)."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    rows, length = x.shape
+    idx = np.zeros((rows, k), dtype=np.int32)
+    val = np.full((rows, k), np.nan, dtype=np.float32)
+    lib().orc_arg_topk(_p(x), _p(val), _p(idx), rows, length, k)
+    return idx, val
 
 
 def traverse_verify_tree(in_tree, out_tree, committed):

@@ -103,3 +103,30 @@ void orc_argmax(float const *in, int *indices, float *prob, int *parent, int row
 }
 
 } // extern "C"
+
+extern "C" {
+
+// ArgTopK::forward_kernel, src/ops/arg_topk.cu:260-371 (heapArgTopK per shard + mergeShards): the min-heap that keeps
+// the k best evicts the HIGHER index among equal values (PreferIndices::kHigher, :272-276, :283-291) and the max-heap
+// that emits them prefers the LOWER index (:299-303), i.e. the output is the first k entries of the row sorted by
+// (value descending, index ascending).  Values are emitted as float for rank < k - 1 only (:318-321, :330-331 is
+// commented out); values[rank k-1] is left as it was.
+void orc_arg_topk(float const *in, float *values, int *indices, int rows, int length, int k) {
+  std::vector<int> order(length);
+  for (int i = 0; i < rows; i++) {
+    float const *p = in + (size_t)i * length;
+    for (int j = 0; j < length; j++) {
+      order[j] = j;
+    }
+    std::partial_sort(order.begin(), order.begin() + k, order.end(),
+                      [&](int a, int b) { return p[a] > p[b] || (p[a] == p[b] && a < b); });
+    for (int r = 0; r < k; r++) {
+      indices[(size_t)i * k + r] = order[r];
+      if (values && r < k - 1) {
+        values[(size_t)i * k + r] = p[order[r]];
+      }
+    }
+  }
+}
+
+} // extern "C"

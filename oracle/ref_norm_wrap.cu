@@ -8,6 +8,7 @@
 // the first helper, C10_WARP_SIZE (:26 of both files), and the launches, which restate forward_kernel of either file
 // (one block per row, min(CUDA_NUM_THREADS = 1024, in_dim) threads).
 #include <algorithm>
+#include <cassert>
 #include <cstdint>
 #include <cub/cub.cuh>
 #include <cuda_fp16.h>
@@ -24,6 +25,12 @@ namespace RefRMSNorm {
 template <typename T>
 #include REF_RMS_INC
 } // namespace RefRMSNorm
+
+// ArgTopK: the whole kernel section of src/ops/arg_topk.cu (from `enum class HeapType` :23 to the end of
+// arg_topk_forward_kernel :371: heap, heapArgTopK, mergeShards, the kernel), streamed by the Makefile.
+namespace RefArgTopK {
+#include REF_ARGTOPK_INC
+} // namespace RefArgTopK
 
 namespace {
 // copy_result, src/ops/argmax.cu:35-47
@@ -51,6 +58,14 @@ int ref_rms_norm_half(void const *x, void const *w, void *out, void *rms_scratch
                       float eps, void *stream) {
   RefRMSNorm::RMSNormFusedForwardKernel<half><<<rows, std::min(1024, dim), 0, (cudaStream_t)stream>>>(
       dim, eps, (half const *)x, (half *)rms_scratch, (half *)norm_scratch, (half const *)w, (half *)out);
+  return (int)cudaGetLastError();
+}
+// ArgTopK::forward_kernel's speculative-decoding launch (src/ops/arg_topk.cu:425-436): one block per row, k threads
+// (num_shards = k), values written for rank < k - 1.
+int ref_arg_topk_half(void const *in, float *values, int *indices, int rows, int length, int k, void *stream) {
+  size_t const shared_memory_size = (size_t)(k + 1) * k * sizeof(RefArgTopK::Entry<half>);
+  RefArgTopK::arg_topk_forward_kernel<half><<<rows, k, 0, (cudaStream_t)stream>>>((half const *)in, shared_memory_size, length, k,
+                                                                               true, values, indices, values != nullptr);
   return (int)cudaGetLastError();
 }
 // offsets_dev: rows + 1 ints {0, length, 2 length, ...}; temp_dev: temp_bytes of scratch (0 / NULL: returns the size

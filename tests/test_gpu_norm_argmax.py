@@ -177,3 +177,50 @@ def test_argmax_equals_the_reference_cub_call(shape):
     torch.cuda.synchronize()
     assert torch.equal(idx, want_idx) and int(idx[0]) == 11
     assert torch.equal(probs, want_prob)
+
+
+@pytest.mark.parametrize("dt", ["half", "bf16"])
+@pytest.mark.parametrize("shape,k", [((16, 32000), 3), ((5, 1001), 2), ((64, 32000), 1), ((3, 50257), 8)])
+def test_arg_topk_bit_exact(dt, shape, k):
+    torch = _torch()
+    from flexflow_b200 import ops
+    rng = np.random.default_rng(shape[0] + k)
+    x = O.from_bits(O.to_bits(rng.standard_normal(shape).astype(np.float32), dt), dt)
+    x[0, [5, shape[1] - 2, 300]] = 40.0   # equal maxima across threads: increasing index order
+    x[1, :] = 1.0                         # all equal: 0, 1, 2, ...
+    want_idx, want_val = O.arg_topk(x, k)
+    tdt = torch.float16 if dt == "half" else torch.bfloat16
+    d = torch.from_numpy(x).cuda().to(tdt)
+    idx = torch.full((shape[0], k), -1, dtype=torch.int32, device="cuda")
+    probs = torch.full((shape[0], k), float("nan"), dtype=torch.float32, device="cuda")
+    ops.ArgTopK.forward_kernel_wrapper(ops.ArgTopKMeta(None, k, speculative_decoding=True), None, d, probs, idx, shape[0])
+    torch.cuda.synchronize()
+    assert np.array_equal(idx.cpu().numpy(), want_idx)
+    got_val = probs.cpu().numpy()
+    assert np.array_equal(got_val[:, :k - 1], want_val[:, :k - 1])           # the ranks the reference writes
+    assert np.array_equal(got_val[:, k - 1], np.take_along_axis(x, want_idx, 1)[:, k - 1])  # and the one it leaves out
+
+
+@needs_ref
+@pytest.mark.parametrize("shape,k", [((16, 32000), 3), ((9, 32000), 2), ((4, 50257), 3)])
+def test_arg_topk_equals_the_reference_kernel(shape, k):
+    """The reference's own heap kernel (arg_topk.cu, k threads per row) on the same rows, ties included."""
+    torch = _torch()
+    from flexflow_b200 import ops
+    ref = O.ref_norm_lib()
+    rows, v = shape
+    g = torch.Generator(device="cuda").manual_seed(rows + k)
+    x = torch.randn(rows, v, generator=g, device="cuda").half()
+    x[0, 11] = x[0, v - 3] = x[0, 500] = 30.0
+    x[1, :] = 0.25
+    want_idx = torch.full((rows, k), -1, dtype=torch.int32, device="cuda")
+    want_val = torch.full((rows, k), float("nan"), dtype=torch.float32, device="cuda")
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    assert ref.ref_arg_topk_half(C.c_void_p(x.data_ptr()), C.c_void_p(want_val.data_ptr()), C.c_void_p(want_idx.data_ptr()),
+                                 rows, v, k, st) == 0
+    idx = torch.full((rows, k), -1, dtype=torch.int32, device="cuda")
+    probs = torch.full((rows, k), float("nan"), dtype=torch.float32, device="cuda")
+    ops.ArgTopK.forward_kernel_wrapper(ops.ArgTopKMeta(None, k, speculative_decoding=True), None, x, probs, idx, rows)
+    torch.cuda.synchronize()
+    assert torch.equal(idx, want_idx), (idx[:2], want_idx[:2])
+    assert torch.equal(probs[:, :k - 1], want_val[:, :k - 1])

@@ -74,3 +74,15 @@ def test_argmax_ties_and_beam_outputs():
     assert np.array_equal(prob, x.max(axis=1)) and not parent.any()
     idx2, prob2, parent2 = O.argmax(x)
     assert np.array_equal(idx2, idx) and prob2 is None and parent2 is None
+
+
+def test_arg_topk_order_and_ties():
+    rng = np.random.default_rng(1)
+    x = rng.standard_normal((6, 5000)).astype(np.float16).astype(np.float32)
+    x[1, [7, 4000, 99]] = 8.0     # three equal maxima: increasing index order
+    x[2, :] = 0.5                 # all equal: 0, 1, 2
+    idx, val = O.arg_topk(x, 3)
+    want = np.argsort(-x, axis=1, kind="stable")[:, :3].astype(np.int32)  # stable: equal values keep index order
+    assert np.array_equal(idx, want)
+    assert list(idx[1]) == [7, 99, 4000] and list(idx[2]) == [0, 1, 2]
+    assert np.array_equal(val[:, :2], np.take_along_axis(x, want, 1)[:, :2]) and np.isnan(val[:, 2]).all()
