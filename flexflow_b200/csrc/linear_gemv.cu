@@ -23,8 +23,8 @@
 // reading epoch e (stream order), so by the time this rank has read everybody's e+1 it may overwrite the e slots.
 #include <cstdlib>
 
-#include "common.cuh"
 #include "peer.h"
+#include "tc_common.cuh"
 
 namespace ffb {
 namespace {
@@ -33,31 +33,6 @@ constexpr int GV_CONSUMERS = 16, GV_THREADS = (GV_CONSUMERS + 1) * 32;
 constexpr int GV_BN = 8;
 constexpr int GV_RING_BYTES = 200 * 1024;
 
-__device__ __forceinline__ uint32_t s_u32(void const *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void gv_mbar_init(uint64_t *bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void gv_expect_tx(uint64_t *bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void gv_arrive(uint64_t *bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(s_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void gv_wait(uint64_t *bar, uint32_t parity) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "GV_WAIT:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra GV_DONE;\n\t"
-      "bra GV_WAIT;\n\t"
-      "GV_DONE:\n\t"
-      "}" ::"r"(s_u32(bar)), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void gv_bulk_g2s(void *dst, void const *src, uint32_t bytes, uint64_t *bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-               ::"r"(s_u32(dst)), "l"(src), "r"(bytes), "r"(s_u32(bar)) : "memory");
-}
 __device__ __forceinline__ void gv_ldsm4(uint32_t addr, uint32_t &r0, uint32_t &r1, uint32_t &r2, uint32_t &r3) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
                : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
@@ -97,8 +72,8 @@ linear_gemv_kernel(T const *__restrict__ A, T const *__restrict__ W, T const *__
 
   if (tid == 0) {
     for (int s = 0; s < STAGES; s++) {
-      gv_mbar_init(&full_bar[s], 1);
-      gv_mbar_init(&empty_bar[s], GV_CONSUMERS);
+      tc::mbar_init(&full_bar[s], 1);
+      tc::mbar_init(&empty_bar[s], GV_CONSUMERS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -116,40 +91,40 @@ linear_gemv_kernel(T const *__restrict__ A, T const *__restrict__ W, T const *__
       int const m0 = M < 8 ? M : 8, m1 = M - m0;
       if (my_tiles > 0) {
         int const n0 = (int)blockIdx.x * GV_BN;
-        gv_expect_tx(&full_bar[2], GV_BN * K * 2);
+        tc::mbar_expect_tx(&full_bar[2], GV_BN * K * 2);
 #pragma unroll
         for (int r = 0; r < GV_BN; r++) {
-          gv_bulk_g2s(ring + 2 * STAGE_BYTES + r * WROW, W + (size_t)(n0 + r) * K, K * 2, &full_bar[2]);
+          tc::bulk_load_1d(ring + 2 * STAGE_BYTES + r * WROW, W + (size_t)(n0 + r) * K, K * 2, &full_bar[2]);
         }
       }
-      gv_expect_tx(&full_bar[0], (uint32_t)(m0 * K * 2));
+      tc::mbar_expect_tx(&full_bar[0], (uint32_t)(m0 * K * 2));
       for (int r = 0; r < m0; r++) {
-        gv_bulk_g2s(ring + (size_t)r * WROW, A + (size_t)r * K, K * 2, &full_bar[0]);
+        tc::bulk_load_1d(ring + (size_t)r * WROW, A + (size_t)r * K, K * 2, &full_bar[0]);
       }
-      gv_expect_tx(&full_bar[1], (uint32_t)(m1 * K * 2));
+      tc::mbar_expect_tx(&full_bar[1], (uint32_t)(m1 * K * 2));
       for (int r = 0; r < m1; r++) {
-        gv_bulk_g2s(ring + (size_t)(8 + r) * WROW, A + (size_t)(8 + r) * K, K * 2, &full_bar[1]);
+        tc::bulk_load_1d(ring + (size_t)(8 + r) * WROW, A + (size_t)(8 + r) * K, K * 2, &full_bar[1]);
       }
       for (int t = 1; t < my_tiles; t++) {
         int const it = t + 2, s = it % STAGES;
         int const n0 = ((int)blockIdx.x + t * (int)gridDim.x) * GV_BN;
-        gv_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
-        gv_expect_tx(&full_bar[s], GV_BN * K * 2);
+        tc::mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
+        tc::mbar_expect_tx(&full_bar[s], GV_BN * K * 2);
 #pragma unroll
         for (int r = 0; r < GV_BN; r++) {
-          gv_bulk_g2s(ring + s * STAGE_BYTES + r * WROW, W + (size_t)(n0 + r) * K, K * 2, &full_bar[s]);
+          tc::bulk_load_1d(ring + s * STAGE_BYTES + r * WROW, W + (size_t)(n0 + r) * K, K * 2, &full_bar[s]);
         }
       }
     }
   } else {
     // ===== consumers: warp w owns k in [w*K/16, (w+1)*K/16) =====
-    uint32_t const ring_addr = s_u32(ring);
+    uint32_t const ring_addr = tc::smem_u32(ring);
     int const g = lane >> 2, tq = lane & 3;
     int const kw = warp * (KSTEPS * 16);
     uint32_t a[KSTEPS][4];
     {
-      gv_wait(&full_bar[0], 0);
-      gv_wait(&full_bar[1], 0);
+      tc::mbar_wait(&full_bar[0], 0);
+      tc::mbar_wait(&full_bar[1], 0);
       int const a_row = (lane & 7) + ((lane >> 3) & 1) * 8, a_kc = (lane >> 4) * 8;
       uint32_t const abase = ring_addr + a_row * WROW + (kw + a_kc) * 2;
 #pragma unroll
@@ -158,8 +133,8 @@ linear_gemv_kernel(T const *__restrict__ A, T const *__restrict__ W, T const *__
       }
       __syncwarp();
       if (lane == 0) {
-        gv_arrive(&empty_bar[0]);
-        gv_arrive(&empty_bar[1]);
+        tc::mbar_arrive(&empty_bar[0]);
+        tc::mbar_arrive(&empty_bar[1]);
       }
     }
     int const b_row = lane & 7, b_kc = (lane >> 3) * 8;
@@ -167,7 +142,7 @@ linear_gemv_kernel(T const *__restrict__ A, T const *__restrict__ W, T const *__
       int const it = t + 2, s = it % STAGES;
       int const n0 = ((int)blockIdx.x + t * (int)gridDim.x) * GV_BN;
       float acc[4] = {0.f, 0.f, 0.f, 0.f};
-      gv_wait(&full_bar[s], (it / STAGES) & 1);
+      tc::mbar_wait(&full_bar[s], (it / STAGES) & 1);
       uint32_t const wbase = ring_addr + s * STAGE_BYTES + b_row * WROW + (kw + b_kc) * 2;
       uint32_t b[KSTEPS / 2][4];
 #pragma unroll
@@ -176,7 +151,7 @@ linear_gemv_kernel(T const *__restrict__ A, T const *__restrict__ W, T const *__
       }
       __syncwarp();
       if (lane == 0) {
-        gv_arrive(&empty_bar[s]); // the tile now lives in registers
+        tc::mbar_arrive(&empty_bar[s]); // the tile now lives in registers
       }
 #pragma unroll
       for (int ks = 0; ks < KSTEPS; ks++) {

@@ -24,6 +24,7 @@
 #include <cstdlib>
 
 #include "dequant.cuh"
+#include "tc_common.cuh"
 
 namespace ffb {
 namespace {
@@ -33,28 +34,6 @@ constexpr int QG_KS = 1024;                // k per stage
 constexpr int QG_RING_BYTES = 160 * 1024;
 constexpr int QG_RED_STRIDE = 36;          // floats per token row of a warp's partial tile (32 + pad)
 
-__device__ __forceinline__ uint32_t qg_s32(void const *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void qg_mbar_init(uint64_t *bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(qg_s32(bar)), "r"(count));
-}
-__device__ __forceinline__ void qg_expect_tx(uint64_t *bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(qg_s32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void qg_wait(uint64_t *bar, uint32_t parity) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "QG_WAIT:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra QG_DONE;\n\t"
-      "bra QG_WAIT;\n\t"
-      "QG_DONE:\n\t"
-      "}" ::"r"(qg_s32(bar)), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void qg_bulk_g2s(void *dst, void const *src, uint32_t bytes, uint64_t *bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-               ::"r"(qg_s32(dst)), "l"(src), "r"(bytes), "r"(qg_s32(bar)) : "memory");
-}
 // barrier over the consumer threads that also ORs a predicate across them
 __device__ __forceinline__ int qg_bar_or(int mine) {
   int res;
@@ -159,7 +138,7 @@ linear_qgemv_kernel(__half const *__restrict__ A, uint8_t const *__restrict__ W,
 
   if (tid == 0) {
     for (int s = 0; s < STAGES; s++) {
-      qg_mbar_init(&full_bar[s], 1);
+      tc::mbar_init(&full_bar[s], 1);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -177,16 +156,16 @@ linear_qgemv_kernel(__half const *__restrict__ A, uint8_t const *__restrict__ W,
     int const gi = (int)blockIdx.x + t * (int)gridDim.x;
     uint8_t *stage = ring + (size_t)s * C::STAGE_BYTES;
     if (warp == 0) { // the transaction count may run negative until this arrives; the phase cannot complete before it
-      qg_expect_tx(&full_bar[s], 32 * C::ROWB + 2 * C::META_BYTES);
+      tc::mbar_expect_tx(&full_bar[s], 32 * C::ROWB + 2 * C::META_BYTES);
       size_t const mrow = (size_t)gi * K + (size_t)st * QG_KS;
-      qg_bulk_g2s(stage + C::VAL_BYTES, offs + mrow, C::META_BYTES, &full_bar[s]);
-      qg_bulk_g2s(stage + C::VAL_BYTES + C::META_BYTES, scales + mrow, C::META_BYTES, &full_bar[s]);
+      tc::bulk_load_1d(stage + C::VAL_BYTES, offs + mrow, C::META_BYTES, &full_bar[s]);
+      tc::bulk_load_1d(stage + C::VAL_BYTES + C::META_BYTES, scales + mrow, C::META_BYTES, &full_bar[s]);
     }
 #pragma unroll
     for (int i = 0; i < 2; i++) { // warp w copies feature rows 2w and 2w + 1
       int const r = 2 * warp + i;
       size_t const e = (size_t)(gi * 32 + r) * K + (size_t)st * QG_KS; // element index of the row segment
-      qg_bulk_g2s(stage + r * C::WROW, W + (QB == 4 ? e / 2 : e), C::ROWB, &full_bar[s]);
+      tc::bulk_load_1d(stage + r * C::WROW, W + (QB == 4 ? e / 2 : e), C::ROWB, &full_bar[s]);
     }
   };
   for (int j = 0; j < STAGES - 1 && j < total_it; j++) {
@@ -220,7 +199,7 @@ linear_qgemv_kernel(__half const *__restrict__ A, uint8_t const *__restrict__ W,
 
   int bad_cur = 0;
   if (total_it > 0) {
-    qg_wait(&full_bar[0], 0);
+    tc::mbar_wait(&full_bar[0], 0);
     bad_cur = qg_bar_or(coef_phase(0, 0));
   }
   for (int t = 0; t < my_tiles; t++) {
@@ -239,7 +218,7 @@ linear_qgemv_kernel(__half const *__restrict__ A, uint8_t const *__restrict__ W,
       }
       if (it + 1 < total_it) { // next stage's coefficients first: its reciprocals are ready when this stage is done
         int const s1 = (it + 1) % STAGES;
-        qg_wait(&full_bar[s1], ((it + 1) / STAGES) & 1);
+        tc::mbar_wait(&full_bar[s1], ((it + 1) / STAGES) & 1);
         bad_next = coef_phase(s1, (it + 1) & 1);
       }
       uint8_t const *stage = ring + (size_t)s * C::STAGE_BYTES;

@@ -1,5 +1,6 @@
 // tc_common.cuh — inline-PTX wrappers for the sm_100a asynchronous machinery shared by the tcgen05 kernels
-// (linear_tc.cu, attn_tc.cu): mbarrier, TMA tensor loads, tcgen05.mma / commit / ld, UMMA descriptors.
+// (linear_tc.cu, linear_tc2.cu, attn_tc.cu) and the bulk-copy weight streams (linear_gemv.cu, linear_qgemv.cu):
+// mbarrier, TMA tensor loads, 1-D bulk copies, tcgen05.mma / commit / ld, UMMA descriptors.
 #pragma once
 #include <cuda.h>
 
@@ -27,6 +28,11 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
       "bra WAIT_LOOP;\n\t"
       "DONE:\n\t"
       "}" ::"r"(addr), "r"(parity) : "memory");
+}
+// 1-D bulk copy global -> shared (16-byte aligned, size a multiple of 16), completion counted on `bar`
+__device__ __forceinline__ void bulk_load_1d(void *dst, void const *src, uint32_t bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void tma_load_2d(void *dst, CUtensorMap const *tm, int c0, int c1, uint64_t *bar) {
   asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
