@@ -148,6 +148,10 @@ def run_ours(args):
     dev = "cuda:%d" % local_rank
     comm = None
     if world > 1:
+        # NCCL writes its version banner to STDOUT at NCCL_DEBUG=VERSION (the box's default); the contract is one JSON
+        # line there.  An explicit INFO / TRACE request is left alone.
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device(dev))
 
         def bcast(b):
