@@ -279,6 +279,117 @@ arg_topk_kernel(T const *__restrict__ in, float *__restrict__ values, int *__res
   }
 }
 
+// k <= KM (the reference's beam widths: <= 3): ONE pass over the row.  Every thread keeps its own KM best entries sorted
+// in registers (a thread meets its entries in increasing index order, so a plain `>` keeps equal values in index order);
+// then k rounds of a block-wide (value desc, index asc) maximum over the threads' current heads, the winner popping its
+// head.  Same result as arg_topk_kernel, a third of its time at k = 3.
+template <typename T, int KM>
+__global__ void __launch_bounds__(1024)
+arg_topk_small_kernel(T const *__restrict__ in, float *__restrict__ values, int *__restrict__ indices, int V, int k) {
+  int const row = blockIdx.x, tid = threadIdx.x, nthr = blockDim.x;
+  T const *p = in + (size_t)row * V;
+  int const nvec = ((size_t)row * V) % 8 == 0 ? V / 8 : 0;
+  float tv[KM];
+  int ti[KM];
+#pragma unroll
+  for (int j = 0; j < KM; j++) {
+    tv[j] = -INFINITY;
+    ti[j] = INT_MAX;
+  }
+  auto insert = [&](float v, int i) {
+    if (!(v > tv[KM - 1])) { // also rejects NaN
+      return;
+    }
+#pragma unroll
+    for (int j = KM - 1; j >= 0; j--) {
+      if (v > tv[j]) { // shift entry j down, take its place (undone by the next iteration if v belongs higher)
+        if (j + 1 < KM) {
+          tv[j + 1] = tv[j];
+          ti[j + 1] = ti[j];
+        }
+        tv[j] = v;
+        ti[j] = i;
+      }
+    }
+  };
+  for (int c0 = tid; c0 < nvec; c0 += 4 * nthr) {
+    uint4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      int const c = c0 + u * nthr;
+      v[u] = c < nvec ? ldg_stream(p + (size_t)c * 8) : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      int const c = c0 + u * nthr;
+      if (c < nvec) {
+        float f[8];
+        unpack8<T>(v[u], f);
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+          insert(f[e], c * 8 + e);
+        }
+      }
+    }
+  }
+  for (int i = nvec * 8 + tid; i < V; i += nthr) {
+    insert(DT<T>::to_f(p[i]), i);
+  }
+  __shared__ float sv[32];
+  __shared__ int si[32];
+  __shared__ int s_win;
+  for (int r = 0; r < k; r++) {
+    float best = tv[0];
+    int bi = ti[0];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      float const ov = __shfl_xor_sync(0xffffffffu, best, o);
+      int const oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ov > best || (ov == best && oi < bi)) {
+        best = ov;
+        bi = oi;
+      }
+    }
+    if ((tid & 31) == 0) {
+      sv[tid >> 5] = best;
+      si[tid >> 5] = bi;
+    }
+    __syncthreads();
+    if (tid < 32) {
+      int const nw = (nthr + 31) >> 5;
+      best = tid < nw ? sv[tid] : -INFINITY;
+      bi = tid < nw ? si[tid] : INT_MAX;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        float const ov = __shfl_xor_sync(0xffffffffu, best, o);
+        int const oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > best || (ov == best && oi < bi)) {
+          best = ov;
+          bi = oi;
+        }
+      }
+      if (tid == 0) {
+        s_win = bi;
+        indices[(size_t)row * k + r] = bi == INT_MAX ? 0 : bi;
+        if (values != nullptr) {
+          values[(size_t)row * k + r] = best;
+        }
+      }
+    }
+    __syncthreads();
+    if (ti[0] == s_win && s_win != INT_MAX) { // the winner pops its head (indices are unique)
+#pragma unroll
+      for (int j = 0; j + 1 < KM; j++) {
+        tv[j] = tv[j + 1];
+        ti[j] = ti[j + 1];
+      }
+      tv[KM - 1] = -INFINITY;
+      ti[KM - 1] = INT_MAX;
+    }
+    __syncthreads(); // s_win is rewritten by the next round
+  }
+}
+
 template <typename T>
 int launch_rms_norm(void const *x1, void const *x2, void const *w, void *res, void *out, int T_rows, int N, float eps,
                     cudaStream_t s) {
@@ -364,12 +475,19 @@ int ffb_arg_topk(void const *input_dev, float *values_dev, int *indices_dev, int
     return FFB_OK;
   }
   int const threads = length >= 8192 ? 1024 : 256;
-  if (dtype == FFB_DT_HALF) {
-    arg_topk_kernel<__half><<<num_tokens, threads, 0, (cudaStream_t)stream>>>((__half const *)input_dev, values_dev,
-                                                                              indices_dev, length, k);
+  cudaStream_t const s = (cudaStream_t)stream;
+  if (k <= 4) {
+    if (dtype == FFB_DT_HALF) {
+      arg_topk_small_kernel<__half, 4><<<num_tokens, threads, 0, s>>>((__half const *)input_dev, values_dev, indices_dev, length, k);
+    } else {
+      arg_topk_small_kernel<__nv_bfloat16, 4><<<num_tokens, threads, 0, s>>>((__nv_bfloat16 const *)input_dev, values_dev,
+                                                                            indices_dev, length, k);
+    }
+  } else if (dtype == FFB_DT_HALF) {
+    arg_topk_kernel<__half><<<num_tokens, threads, 0, s>>>((__half const *)input_dev, values_dev, indices_dev, length, k);
   } else {
-    arg_topk_kernel<__nv_bfloat16><<<num_tokens, threads, 0, (cudaStream_t)stream>>>((__nv_bfloat16 const *)input_dev,
-                                                                                     values_dev, indices_dev, length, k);
+    arg_topk_kernel<__nv_bfloat16><<<num_tokens, threads, 0, s>>>((__nv_bfloat16 const *)input_dev, values_dev, indices_dev,
+                                                                  length, k);
   }
   FFB_LAUNCH_CHECK();
   return FFB_OK;
