@@ -168,6 +168,47 @@ inline void inference_kernel_wrapper(AllReduceMeta const *m, ffb_batch_config co
   check(ffb_allreduce(m->handle.ncclComm, input.ptr, output.ptr, num_elements, input.data_type, stream), "ffb_allreduce");
 }
 } // namespace AllReduce
+
+// The row operators either side of the chain.
+namespace ResidualRMSNorm {
+struct ResidualRMSNormMeta { // include/flexflow/ops/residual_rms_norm.h: eps, in_dim, batch_size
+  float eps;
+  int in_dim;
+};
+// Kernels::ResidualRMSNorm::inference_kernel_wrapper (src/ops/kernels/residual_rms_norm_kernels.cu:205-232)
+inline void inference_kernel_wrapper(ResidualRMSNormMeta *m, ffb_batch_config const *bc,
+                                     GenericTensorAccessorR const &input1, GenericTensorAccessorR const &input2,
+                                     GenericTensorAccessorR const &weight, GenericTensorAccessorW const &residual_output,
+                                     GenericTensorAccessorW const &output, ffb_stream_t stream) {
+  check(ffb_residual_rms_norm(input1.ptr, input2.ptr, weight.ptr, residual_output.ptr, output.ptr, bc->num_tokens,
+                              m->in_dim, m->eps, output.data_type, stream), "ffb_residual_rms_norm");
+}
+} // namespace ResidualRMSNorm
+namespace RMSNorm {
+// Kernels::RMSNorm::inference_kernel_wrapper (src/ops/kernels/rms_norm_kernels.cu:148-190)
+inline void inference_kernel_wrapper(ResidualRMSNorm::ResidualRMSNormMeta *m, ffb_batch_config const *bc,
+                                     GenericTensorAccessorR const &input, GenericTensorAccessorR const &weight,
+                                     GenericTensorAccessorW const &output, ffb_stream_t stream) {
+  check(ffb_residual_rms_norm(input.ptr, nullptr, weight.ptr, nullptr, output.ptr, bc->num_tokens, m->in_dim, m->eps,
+                              output.data_type, stream), "ffb_residual_rms_norm");
+}
+} // namespace RMSNorm
 } // namespace Kernels
+
+// ArgMax::forward_kernel_wrapper (src/ops/argmax.cu:156-206) / ArgTopK::forward_kernel_wrapper (src/ops/arg_topk.cu:451-541)
+struct ArgMax {
+  static void forward_kernel_wrapper(bool beam_search, GenericTensorAccessorR const &input, int *indices, float *probs,
+                                     int *parent, int batch_size, int length, ffb_stream_t stream) {
+    check(ffb_argmax(input.ptr, indices, beam_search ? probs : nullptr, beam_search ? parent : nullptr, batch_size, length,
+                     input.data_type, stream), "ffb_argmax");
+  }
+};
+struct ArgTopK {
+  static void forward_kernel_wrapper(bool speculative_decoding, GenericTensorAccessorR const &input, float *probs,
+                                     int *indices, int batch_size, int length, int k, ffb_stream_t stream) {
+    check(ffb_arg_topk(input.ptr, speculative_decoding ? probs : nullptr, indices, batch_size, length, k, input.data_type,
+                       stream), "ffb_arg_topk");
+  }
+};
 
 } // namespace ffb

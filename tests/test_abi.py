@@ -110,3 +110,11 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 txt = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "oracle" not in txt.lower().replace("no cpu", ""), os.path.join(dirpath, f)
+
+
+def test_cpp_host_mirror_compiles(tmp_path):
+    """flexflow_b200/host/ffb_ops.h (the C++ layer with the reference's class / function names) against include/ffb200.h."""
+    src = tmp_path / "use_ops.cc"
+    src.write_text('#include "ffb_ops.h"\nint main() { return sizeof(ffb::FFHandler) > 0 ? 0 : 1; }\n')
+    subprocess.run(["g++", "-std=c++17", "-fsyntax-only", "-I", os.path.join(ROOT, "include"),
+                    "-I", os.path.join(ROOT, "flexflow_b200", "host"), str(src)], check=True)
