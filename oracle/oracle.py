@@ -84,6 +84,22 @@ def ref_norm_lib():
     return _ref_norm
 
 
+_REF_LINEAR_SO = os.path.join(_HERE, "_ref", "libref_linear.so")
+_ref_linear = None
+
+
+def ref_linear_lib():
+    """The reference Linear's cublasGemmEx call (fp16 accumulation) restated, or None when the .so was not built."""
+    global _ref_linear
+    if _ref_linear is None and os.path.exists(_REF_LINEAR_SO):
+        try:
+            _ref_linear = C.CDLL(_REF_LINEAR_SO)
+        except OSError:  # no cuBLAS on this machine
+            return None
+        _ref_linear.ref_linear_forward_half.argtypes = [C.c_void_p] * 3 + [C.c_int] * 3 + [C.c_void_p]
+    return _ref_linear
+
+
 def lib():
     global _lib
     if _lib is None:

@@ -353,3 +353,36 @@ def test_oracle_and_kernels_agree_with_the_reference_kernel_on_edge_scales(bits)
     for name, x in (("kernel", got), ("oracle", orc)):
         assert (np.isnan(x.view(np.float16)) == nan_w).all(), name
         assert (x[~nan_w] == want[~nan_w]).all(), name
+
+
+# ---- the reference Linear's own GEMM call (cublasGemmEx, fp16 accumulation) restated in oracle/_ref/libref_linear.so ----
+needs_ref_linear = pytest.mark.skipif(O.ref_linear_lib() is None, reason="oracle/_ref/libref_linear.so not built")
+
+
+@needs_ref_linear
+@pytest.mark.parametrize("M", [1, 16, 64, 200, 512])
+@pytest.mark.parametrize("K,N", [(4096, 12288), (4096, 4096)])
+def test_linear_against_the_reference_cublas_call(M, K, N):
+    """Every dispatch range of ffb_linear_forward (GEMV, tcgen05 1-SM and SM-pair kernels) against the call the
+    reference makes.  The reference accumulates in fp16 (compute type = DT), the product in fp32, so the product must
+    sit closer to the fp32 oracle than the reference does, and the two must agree within the reference's own error."""
+    torch = _torch()
+    from flexflow_b200 import ops
+    ref = O.ref_linear_lib()
+    g = torch.Generator(device="cuda").manual_seed(M + N)
+    x = torch.randn(M, K, generator=g, device="cuda").half()
+    w = (torch.randn(N, K, generator=g, device="cuda") * 0.02).half()
+    m = ops.LinearMeta(ops.FFHandler("cuda:0"), K, N, max_tokens_per_batch=1024)
+    got = torch.empty(M, N, dtype=torch.float16, device="cuda")
+    ops.Linear.inference_kernel_wrapper(m, None, x, got, w, None, K, N, M)
+    want = torch.empty(M, N, dtype=torch.float16, device="cuda")
+    assert ref.ref_linear_forward_half(C.c_void_p(x.data_ptr()), C.c_void_p(w.data_ptr()), C.c_void_p(want.data_ptr()), K, N, M,
+                                       C.c_void_p(torch.cuda.current_stream().cuda_stream)) == 0
+    torch.cuda.synchronize()
+    exact = x.double() @ w.double().t()
+    scale = exact.abs().max().item()
+    err_ours = (got.double() - exact).abs().max().item() / scale
+    err_ref = (want.double() - exact).abs().max().item() / scale
+    assert err_ours < 2e-3, err_ours
+    assert err_ours <= err_ref + 1e-4, (err_ours, err_ref)
+    assert (got.double() - want.double()).abs().max().item() / scale < 1e-2 + 2 * err_ref

@@ -31,6 +31,17 @@ def time_ms(fn, iters=20, warm=3):
     return e0.elapsed_time(e1) / iters
 
 
+def _ref_linear():
+    try:
+        from oracle import oracle as O  # loader of oracle/_ref only
+        return O.ref_linear_lib()
+    except Exception:  # noqa: BLE001
+        return None
+
+
+REF_LINEAR = _ref_linear()
+
+
 def main():
     h = ops.FFHandler("cuda:0")
     res = []
@@ -60,6 +71,17 @@ def main():
             flops = 2.0 * M * K * N
             res.append(dict(layer=name, M=M, K=K, N=N, ms=ms, tflops=flops / ms / 1e9, weight_gbs=K * N * 2 / ms / 1e6,
                             cublas_ms=ref, cublas_tflops=flops / ref / 1e9))
+            if REF_LINEAR is not None:  # the reference's own call: cublasGemmEx with fp16 accumulation
+                import ctypes as C
+                k2 = [0]
+
+                def ref16_fn():
+                    k2[0] += 1
+                    REF_LINEAR.ref_linear_forward_half(C.c_void_p(x.data_ptr()), C.c_void_p(ws[k2[0] % 4].data_ptr()),
+                                                       C.c_void_p(out.data_ptr()), K, N, M,
+                                                       C.c_void_p(torch.cuda.current_stream().cuda_stream))
+                r16 = time_ms(ref16_fn)
+                res[-1].update(reference_cublas16f_ms=r16, reference_cublas16f_tflops=flops / r16 / 1e9)
             print(res[-1], flush=True)
     if "--json" in sys.argv:
         json.dump(res, open(sys.argv[sys.argv.index("--json") + 1], "w"), indent=1)
