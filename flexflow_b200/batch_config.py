@@ -140,6 +140,18 @@ class CombinedBatchConfigMeta(C.Structure):
     ]
 
 
+class InferenceResult(C.Structure):
+    """include/flexflow/batch_config.h:166-170"""
+    _fields_ = [("token_ids", C.c_int * MAX_NUM_TOKENS), ("finetuning_loss", C.c_float)]
+
+
+class BeamInferenceResult(C.Structure):
+    """include/flexflow/batch_config.h:231-240"""
+    _fields_ = [("token_ids", C.c_int * (MAX_NUM_TOKENS * MAX_SPECULATIVE_TREE_BRANCHES)),
+                ("probs", C.c_float * (MAX_NUM_TOKENS * MAX_SPECULATIVE_TREE_BRANCHES)),
+                ("parent_id", C.c_int * (MAX_NUM_TOKENS * MAX_SPECULATIVE_TREE_BRANCHES))]
+
+
 assert C.sizeof(PerRequestInfo) == 1072
 assert C.sizeof(BitMask) == 528
 assert C.sizeof(BatchConfig) == 128736

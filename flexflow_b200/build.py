@@ -27,6 +27,7 @@ SOURCES = [
     "comm.cu",
     "norm_argmax.cu",
     "host_tree.cu",
+    "request_manager.cu",
 ]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -30,6 +30,12 @@ class AttnDesc(C.Structure):
     ]
 
 
+class RMDesc(C.Structure):
+    _fields_ = [("max_requests_per_batch", C.c_int), ("max_tokens_per_batch", C.c_int),
+                ("max_spec_tree_token_num", C.c_int), ("max_sequence_length", C.c_int), ("num_ssms", C.c_int),
+                ("num_eos_tokens", C.c_int), ("eos_token_ids", C.c_int * 8)]
+
+
 class LinearDesc(C.Structure):
     _fields_ = [("dtype", C.c_int), ("quant_type", C.c_int), ("in_dim", C.c_int), ("out_dim", C.c_int),
                 ("max_batch", C.c_int), ("activation", C.c_int)]
@@ -73,6 +79,21 @@ SIGNATURES = {
     "ffb_bitmask_append_pending": (None, [_vp, _i]),
     "ffb_bitmask_append": (_i, [_vp, _i, _vp, _i]),
     "ffb_traverse_verify_tree": (_i, [_vp, _i, _vp, _i, _vp, _vp, C.POINTER(_i), _vp, C.POINTER(_i)]),
+    "ffb_rm_create": (_i, [C.POINTER(RMDesc), C.POINTER(_vp)]),
+    "ffb_rm_destroy": (_i, [_vp]),
+    "ffb_rm_push_spec_infer_tree_width": (_i, [_vp, _i]),
+    "ffb_rm_register_request": (_i, [_vp, _vp, _i, _i, _i, C.POINTER(_sz)]),
+    "ffb_rm_prepare_next_batch": (_i, [_vp, _vp, _vp, _vp]),
+    "ffb_rm_prepare_next_batch_init": (_i, [_vp, _vp, _vp, _i, _vp]),
+    "ffb_rm_prepare_next_batch_beam": (_i, [_vp, _vp, _vp, _vp]),
+    "ffb_rm_prepare_next_batch_verify": (_i, [_vp, _vp, _i, _vp]),
+    "ffb_rm_request_status": (_i, [_vp, _sz, C.POINTER(_i)]),
+    "ffb_rm_request_tokens": (_i, [_vp, _sz, _vp, _i, C.POINTER(_i)]),
+    "ffb_rm_request_steps": (_i, [_vp, _sz, C.POINTER(_i), C.POINTER(_i)]),
+    "ffb_rm_num_pending": (_i, [_vp]),
+    "ffb_rm_num_processed_requests": (_sz, [_vp]),
+    "ffb_fetch_inference_result": (_i, [_vp, _i, _vp, _vp]),
+    "ffb_fetch_beam_inference_result": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
 }
 
 _lib = None

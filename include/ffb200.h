@@ -239,6 +239,78 @@ int ffb_traverse_verify_tree(ffb_tree_node const *input_tree, int n_in, ffb_tree
                              ffb_commit_entry const *committed_in, ffb_tree_node *verified, int *n_verified,
                              ffb_commit_entry *committed_out, int *n_committed);
 
+/* ---- serving control: the batch builders of RequestManager -------------------------------------------
+ * Host code, integer only.  One handle plays the role of the RequestManager singleton: the request table
+ * (all_requests, pending_infr_request_queue), each request's speculation tree (Request::beam_trees), the serialised
+ * tree handed to the verifier (dfs_tree_inputs) and the commit list (committed_tokens).  The four builders consume the
+ * previous batch descriptor plus the model's result and fill the next descriptor in the reference's layout
+ * (include/ffb200_batch_config.h), field for field what the reference's functions emit:
+ *   ffb_rm_prepare_next_batch         RequestManager::prepare_next_batch        src/runtime/request_manager.cc:713-1138
+ *   ffb_rm_prepare_next_batch_init    ...::prepare_next_batch_init              :1170-1580
+ *   ffb_rm_prepare_next_batch_beam    ...::prepare_next_batch_beam (+ store_beam_metadata / update_beam_metadata
+ *                                     :2217-2379)                                :1610-1892
+ *   ffb_rm_prepare_next_batch_verify  ...::prepare_next_batch_verify (+ traverse_beam_tree / merge_dfs_trees
+ *                                     :2743-2888)                                :1923-2215
+ * One SpecInfer round is serve_spec_infer's (:3083-3173): init -> FFB_MAX_BEAM_DEPTH x (SSM step, beam) -> verify -> LLM
+ * step.  Fields the reference leaves uninitialised (request_running in incremental mode, beam tokens / probs /
+ * parent_id of slots that do not use them, ...) are zero here.  PEFT / fine-tuning requests are out of scope
+ * (FFB_ERR_UNSUPPORTED never arises: they cannot be registered).  Where the reference asserts, these return
+ * FFB_ERR_STATE / FFB_ERR_INVALID and leave *new_bc unspecified. */
+typedef struct {
+  int max_requests_per_batch;  /* RequestManager::set_max_requests_per_batch, request_manager.cc:117-122 */
+  int max_tokens_per_batch;
+  int max_spec_tree_token_num;
+  int max_sequence_length;
+  int num_ssms;                /* register_ssm_model calls (0: incremental decoding only) */
+  int num_eos_tokens;          /* eos_token_ids, request_manager.cc:181-244 */
+  int eos_token_ids[8];
+} ffb_rm_desc;
+typedef struct ffb_rm_s *ffb_rm_t;
+enum { FFB_REQ_PENDING = 101, FFB_REQ_RUNNING = 102, FFB_REQ_COMPLETED = 103, FFB_REQ_FINISHING = 104 }; /* Request::Status */
+
+/* BeamInferenceResult, include/flexflow/batch_config.h:231-240 */
+typedef struct {
+  int token_ids[FFB_MAX_NUM_TOKENS * FFB_MAX_SPECULATIVE_TREE_BRANCHES];
+  float probs[FFB_MAX_NUM_TOKENS * FFB_MAX_SPECULATIVE_TREE_BRANCHES];
+  int parent_id[FFB_MAX_NUM_TOKENS * FFB_MAX_SPECULATIVE_TREE_BRANCHES];
+} ffb_beam_inference_result;
+
+int ffb_rm_create(ffb_rm_desc const *desc, ffb_rm_t *out);
+int ffb_rm_destroy(ffb_rm_t rm);
+/* RequestManager::push_spec_infer_tree_width (request_manager.cc:168-171): beam width of SSM step k of every round. */
+int ffb_rm_push_spec_infer_tree_width(ffb_rm_t rm, int tree_width);
+/* RequestManager::register_new_request (request_manager.cc:334-441) for already tokenised prompts: max_length /
+ * max_new_tokens follow its rules (-1 = unset; both unset: max_sequence_length - 1; max_new_tokens wins).  A prompt or
+ * max_length that does not fit max_sequence_length gives FFB_ERR_INVALID (the reference returns INVALID_GUID). */
+int ffb_rm_register_request(ffb_rm_t rm, int const *prompt_tokens, int num_tokens, int max_length, int max_new_tokens,
+                            size_t *guid_out);
+int ffb_rm_prepare_next_batch(ffb_rm_t rm, ffb_batch_config const *old_bc, ffb_inference_result const *result,
+                              ffb_batch_config *new_bc);
+int ffb_rm_prepare_next_batch_init(ffb_rm_t rm, ffb_tree_verify_batch_config const *old_bc,
+                                   ffb_inference_result const *result, int model_id,
+                                   ffb_beam_search_batch_config *new_bc);
+int ffb_rm_prepare_next_batch_beam(ffb_rm_t rm, ffb_beam_search_batch_config const *old_bc,
+                                   ffb_beam_inference_result const *result, ffb_beam_search_batch_config *new_bc);
+int ffb_rm_prepare_next_batch_verify(ffb_rm_t rm, ffb_beam_search_batch_config const *const *old_batches,
+                                     int num_batches, ffb_tree_verify_batch_config *new_bc);
+/* Request state: status (Request::Status), the token sequence so far (copies min(n, capacity) ids, *num_tokens = n),
+ * profiling counters (ProfileInfo::llm_decoding_steps / ssm_decoding_steps). */
+int ffb_rm_request_status(ffb_rm_t rm, size_t guid, int *status_out);
+int ffb_rm_request_tokens(ffb_rm_t rm, size_t guid, int *tokens_out, int capacity, int *num_tokens);
+int ffb_rm_request_steps(ffb_rm_t rm, size_t guid, int *llm_decoding_steps, int *ssm_decoding_steps);
+int ffb_rm_num_pending(ffb_rm_t rm);
+size_t ffb_rm_num_processed_requests(ffb_rm_t rm);
+
+/* The D2H that ends a model step: ArgMax::inference_task / ArgTopK::inference_speculative_task copy the
+ * token ids (and, in beam mode, the probabilities) of the step into the InferenceResult the next builder reads
+ * (src/ops/argmax.cc:300-372, src/ops/arg_topk.cc:395-437).  One (two) cudaMemcpyAsync on `stream` followed by a
+ * stream synchronise - the call returns with the host struct filled, like the reference's copy_tensor_dev_to_host.
+ * parent_id, which the reference leaves unwritten, is zero-filled for the entries copied. */
+int ffb_fetch_inference_result(int const *indices_dev, int num_tokens, ffb_inference_result *result_host,
+                               ffb_stream_t stream);
+int ffb_fetch_beam_inference_result(int const *indices_dev, float const *probs_dev, int num_tokens, int k,
+                                    ffb_beam_inference_result *result_host, ffb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
