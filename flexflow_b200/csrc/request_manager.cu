@@ -2,8 +2,8 @@
 // incremental decoding (prepare_next_batch, src/runtime/request_manager.cc:713-1138) and the three SpecInfer builders
 // (prepare_next_batch_init :1170-1580, _beam :1610-1892 with store/update_beam_metadata :2217-2379, _verify :1923-2215
 // with traverse_beam_tree / merge_dfs_trees :2743-2888).  They emit the reference's descriptors field for field
-// (tests/test_request_manager.py runs them in lockstep with the reference's own functions compiled into
-// oracle/_ref/libref_host.so), but are organised differently: requests live in a flat table indexed by guid - first
+// (tests/test_request_manager.py runs them in lockstep with the reference's own functions, compiled from the reference
+// tree by the test infrastructure), but are organised differently: requests live in a flat table indexed by guid - first
 // guid, a request's speculation tree is a short array of layers, descriptors are zero-filled PODs, every reference
 // assert is a returned status.  Also here: the D2H that ends a model step (InferenceResult / BeamInferenceResult).
 #include <algorithm>
