@@ -429,11 +429,7 @@ int launch_multi_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta,
 #define FFB_MQ(TT, DH)                                                                                     \
   do {                                                                                                     \
     size_t const smem = (size_t)(BM + 4 * BN) * DH * 2;                                                    \
-    static bool attr_set = false;                                                                          \
-    if (!attr_set) {                                                                                       \
-      FFB_CUDA_TRY(cudaFuncSetAttribute(multi_attn_kernel<TT, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-      attr_set = true;                                                                                     \
-    }                                                                                                      \
+    FFB_SET_MAX_SMEM_ONCE((multi_attn_kernel<TT, DH>), smem);                                              \
     multi_attn_kernel<TT, DH><<<grid, MQ_THREADS, smem, s>>>(                                              \
         (TT const *)h->q_buf, (TT const *)h->k_cache, (TT const *)h->v_cache, h->qdesc, meta, h->partial,  \
         h->split_counter, (TT *)out, d.mode, d.num_q_heads, d.num_kv_heads, h->cache_len, m_tiles, chunk, nsplit, \

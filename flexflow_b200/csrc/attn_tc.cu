@@ -865,11 +865,7 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
 #define FFB_ATC(TT, DH)                                                                                              \
   do {                                                                                                               \
     size_t const smem = AtcCfg<DH>::SMEM;                                                                            \
-    static bool attr_set = false;                                                                                    \
-    if (!attr_set) {                                                                                                 \
-      FFB_CUDA_TRY(cudaFuncSetAttribute(attn_tc_kernel<TT, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-      attr_set = true;                                                                                               \
-    }                                                                                                                \
+    FFB_SET_MAX_SMEM_ONCE((attn_tc_kernel<TT, DH>), smem);                                                           \
     attn_tc_kernel<TT, DH><<<grid, ATC_THREADS, smem, s>>>(tmK, tmV, sc, (TT const *)h->q_buf, h->qdesc, meta,       \
                                                             h->partial, h->split_counter, (TT *)out, d.num_q_heads,   \
                                                             d.num_kv_heads, h->cache_len, scale_log2, tracing ? trace : nullptr); \

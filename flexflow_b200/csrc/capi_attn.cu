@@ -9,6 +9,9 @@
 #include <cstring>
 #include <new>
 
+#include <mutex>
+#include <vector>
+
 #include "attn_state.h"
 
 namespace ffb {
@@ -177,12 +180,68 @@ int ffb_attn_last_kernel_ms(ffb_attn_t h, float *ms) {
   return FFB_OK;
 }
 
+} // extern "C"
+
+namespace {
+// fence events of the staging blocks handed to ffb_load_batch_config, keyed by (block, device)
+struct StagingFence {
+  void *staging;
+  int device;
+  cudaEvent_t ev;
+};
+std::mutex g_fence_mu;
+std::vector<StagingFence> g_fences;
+
+// Waits until the previous upload from `staging` on the current device has been executed and returns the event to
+// record after the next one.
+int staging_fence(void *staging, cudaEvent_t *out) {
+  int dev = 0;
+  FFB_CUDA_TRY(cudaGetDevice(&dev));
+  cudaEvent_t ev = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_fence_mu);
+    for (StagingFence const &f : g_fences) {
+      if (f.staging == staging && f.device == dev) {
+        ev = f.ev;
+        break;
+      }
+    }
+    if (!ev) {
+      FFB_CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+      g_fences.push_back(StagingFence{staging, dev, ev});
+      *out = ev;
+      return FFB_OK; // first use of this block: nothing in flight
+    }
+  }
+  FFB_CUDA_TRY(cudaEventSynchronize(ev));
+  *out = ev;
+  return FFB_OK;
+}
+} // namespace
+
+extern "C" {
+
 int ffb_load_batch_config(void const *bc_host, int mode, void *staging, ffb_combined_batch_config_meta *meta_dev,
                           ffb_stream_t stream) {
   FFB_REQUIRE(bc_host && staging && meta_dev, "null argument");
   ffb_batch_config const *bc = (ffb_batch_config const *)bc_host;
   ffb_combined_batch_config_meta *st = (ffb_combined_batch_config_meta *)staging;
   FFB_REQUIRE(bc->num_tokens >= 0 && bc->num_tokens <= FFB_MAX_NUM_TOKENS, "num_tokens %d out of range", bc->num_tokens);
+  // The copy below is truly asynchronous (pinned source), unlike the reference's pageable copies, which the driver
+  // stages before returning: a host that runs ahead of the stream must not repack a staging block whose previous
+  // copy has not run yet.  Each (staging block, device) pair therefore carries a fence event, recorded after its copy
+  // and waited for here before the block is written again.  (Skipped under stream capture: events recorded into a
+  // graph cannot be waited for from the host; a captured upload replays its capture-time bytes anyway.)
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing((cudaStream_t)stream, &cap);
+  bool const capturing = cap != cudaStreamCaptureStatusNone;
+  cudaEvent_t fence = nullptr;
+  if (!capturing) {
+    int rc = staging_fence(staging, &fence);
+    if (rc != FFB_OK) {
+      return rc;
+    }
+  }
   // request_manager.cu:98-164 copies the same members one cudaMemcpyAsync at a time
   memcpy(st->tokens_info, bc->tokensInfo, sizeof(ffb_per_token_info) * (size_t)bc->num_tokens);
   memcpy(st->requestsInfo, bc->requestsInfo, sizeof(st->requestsInfo));
@@ -203,6 +262,9 @@ int ffb_load_batch_config(void const *bc_host, int mode, void *staging, ffb_comb
     FFB_REQUIRE(mode == FFB_INC_DECODING_MODE, "unknown inference mode %d", mode);
   }
   FFB_CUDA_TRY(cudaMemcpyAsync(meta_dev, st, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+  if (fence && !capturing) {
+    FFB_CUDA_TRY(cudaEventRecord(fence, (cudaStream_t)stream));
+  }
   return FFB_OK;
 }
 

@@ -29,27 +29,28 @@ struct NcclApi {
   char const *(*GetErrorString)(int) = nullptr;
 };
 
-NcclApi *nccl() {
-  static NcclApi api;
-  static bool tried = false;
-  if (!tried) {
-    tried = true;
-    char const *names[] = {"libnccl.so.2", "libnccl.so"};
-    for (char const *n : names) {
-      api.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
-      if (api.lib) {
-        break;
-      }
-    }
+NcclApi load_nccl() {
+  NcclApi api;
+  char const *names[] = {"libnccl.so.2", "libnccl.so"};
+  for (char const *n : names) {
+    api.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
     if (api.lib) {
-      api.GetUniqueId = (decltype(api.GetUniqueId))dlsym(api.lib, "ncclGetUniqueId");
-      api.CommInitRank = (decltype(api.CommInitRank))dlsym(api.lib, "ncclCommInitRank");
-      api.CommDestroy = (decltype(api.CommDestroy))dlsym(api.lib, "ncclCommDestroy");
-      api.AllReduce = (decltype(api.AllReduce))dlsym(api.lib, "ncclAllReduce");
-      api.AllGather = (decltype(api.AllGather))dlsym(api.lib, "ncclAllGather");
-      api.GetErrorString = (decltype(api.GetErrorString))dlsym(api.lib, "ncclGetErrorString");
+      break;
     }
   }
+  if (api.lib) {
+    api.GetUniqueId = (decltype(api.GetUniqueId))dlsym(api.lib, "ncclGetUniqueId");
+    api.CommInitRank = (decltype(api.CommInitRank))dlsym(api.lib, "ncclCommInitRank");
+    api.CommDestroy = (decltype(api.CommDestroy))dlsym(api.lib, "ncclCommDestroy");
+    api.AllReduce = (decltype(api.AllReduce))dlsym(api.lib, "ncclAllReduce");
+    api.AllGather = (decltype(api.AllGather))dlsym(api.lib, "ncclAllGather");
+    api.GetErrorString = (decltype(api.GetErrorString))dlsym(api.lib, "ncclGetErrorString");
+  }
+  return api;
+}
+
+NcclApi *nccl() {
+  static NcclApi api = load_nccl(); // initialised once, thread-safe (C++11)
   if (!api.lib || !api.GetUniqueId || !api.CommInitRank || !api.CommDestroy || !api.AllReduce) {
     ffb::set_error("NCCL (libnccl.so.2) could not be loaded: %s", dlerror());
     return nullptr;
@@ -87,42 +88,64 @@ namespace {
 
 constexpr int kPeerMaxN = 8192; // widest hidden size served by the fused path (LLaMA-2-70B)
 
-// Best effort: on any failure the communicator simply has no peer table and every collective goes through NCCL.
+// Best effort, but AGREED: every rank of a communicator ends up with the same peer_ok, because a rank that launched the
+// fused peer-push kernel while another fell back to NCCL would spin forever.  All ranks therefore take part in every
+// collective below whatever happened locally (the only early return, on the rank-independent conditions nranks /
+// AllGather availability, is taken by all ranks alike); local failures - allocation, IPC export or open, or
+// FFB_DISABLE_PEER set in this rank's environment - travel in an ok flag that is min-reduced across ranks at the end.
 void peer_setup(ffb_comm_s *c, NcclApi *api) {
   using namespace ffb;
-  if (c->nranks < 2 || c->nranks > kPeerMaxRanks || !api->AllGather || getenv("FFB_DISABLE_PEER")) {
+  if (c->nranks < 2 || c->nranks > kPeerMaxRanks || !api->AllGather) {
     return;
   }
   size_t const recv_bytes = (size_t)2 * c->nranks * kPeerMaxTokens * kPeerMaxN * 2 * sizeof(float); // {value, epoch}
   size_t const flag_bytes = (size_t)c->nranks * kPeerMaxCtas * sizeof(int);
   size_t const total = recv_bytes + flag_bytes + 256;
-  cudaIpcMemHandle_t mine, *all_dev = nullptr, all[kPeerMaxRanks];
-  if (cudaMalloc(&c->peer_local, total) != cudaSuccess) {
+  struct Rec {
+    cudaIpcMemHandle_t handle;
+    int ok;
+  };
+  Rec mine, all[kPeerMaxRanks];
+  memset(&mine, 0, sizeof(mine));
+  bool ok = getenv("FFB_DISABLE_PEER") == nullptr;
+  if (ok && cudaMalloc(&c->peer_local, total) != cudaSuccess) {
     c->peer_local = nullptr;
     cudaGetLastError();
-    return;
+    ok = false;
   }
-  bool ok = cudaMemset(c->peer_local, 0, total) == cudaSuccess && cudaIpcGetMemHandle(&mine, c->peer_local) == cudaSuccess &&
-            cudaMalloc(&all_dev, sizeof(mine) * (c->nranks + 1)) == cudaSuccess;
-  if (ok) {
-    ok = cudaMemcpy(all_dev + c->nranks, &mine, sizeof(mine), cudaMemcpyHostToDevice) == cudaSuccess &&
-         api->AllGather(all_dev + c->nranks, all_dev, sizeof(mine), /*ncclInt8*/ 0, c->comm, nullptr) == ncclSuccess &&
-         cudaStreamSynchronize(nullptr) == cudaSuccess &&
-         cudaMemcpy(all, all_dev, sizeof(mine) * c->nranks, cudaMemcpyDeviceToHost) == cudaSuccess;
+  ok = ok && cudaMemset(c->peer_local, 0, total) == cudaSuccess && cudaIpcGetMemHandle(&mine.handle, c->peer_local) == cudaSuccess;
+  mine.ok = ok ? 1 : 0;
+  // exchange {handle, ok}: a few hundred bytes of device scratch; without it this rank cannot take part at all
+  Rec *scratch = nullptr;
+  if (cudaMalloc(&scratch, sizeof(Rec) * (c->nranks + 1)) != cudaSuccess) {
+    cudaGetLastError();
+    return; // (the other ranks would wait in the AllGather: there is nothing left to do for a process this starved)
   }
-  if (all_dev) {
-    cudaFree(all_dev);
+  bool exchanged = cudaMemcpy(scratch + c->nranks, &mine, sizeof(mine), cudaMemcpyHostToDevice) == cudaSuccess;
+  exchanged = (api->AllGather(scratch + c->nranks, scratch, sizeof(Rec), /*ncclInt8*/ 0, c->comm, nullptr) == ncclSuccess) && exchanged;
+  exchanged = exchanged && cudaStreamSynchronize(nullptr) == cudaSuccess &&
+              cudaMemcpy(all, scratch, sizeof(Rec) * c->nranks, cudaMemcpyDeviceToHost) == cudaSuccess;
+  ok = ok && exchanged;
+  for (int r = 0; exchanged && r < c->nranks; r++) {
+    ok = ok && all[r].ok != 0;
   }
   for (int r = 0; ok && r < c->nranks; r++) {
     void *base = c->peer_local;
     if (r != c->rank) {
-      ok = cudaIpcOpenMemHandle(&c->peer_mapped[r], all[r], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+      ok = cudaIpcOpenMemHandle(&c->peer_mapped[r], all[r].handle, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
       base = c->peer_mapped[r];
     }
     c->peer.recv[r] = (float *)base;
     c->peer.flags[r] = (int *)((char *)base + recv_bytes);
   }
-  if (!ok) {
+  // second agreement: did EVERY rank map every area?
+  int flag = ok ? 1 : 0;
+  bool agreed = cudaMemcpy(scratch, &flag, sizeof(int), cudaMemcpyHostToDevice) == cudaSuccess;
+  agreed = (api->AllReduce(scratch, scratch, 1, /*ncclInt32*/ 2, /*ncclMin*/ 3, c->comm, nullptr) == ncclSuccess) && agreed;
+  agreed = agreed && cudaStreamSynchronize(nullptr) == cudaSuccess &&
+           cudaMemcpy(&flag, scratch, sizeof(int), cudaMemcpyDeviceToHost) == cudaSuccess;
+  cudaFree(scratch);
+  if (!agreed || flag == 0) {
     cudaGetLastError();
     return; // mappings (if any) are released in ffb_comm_destroy
   }

@@ -5,6 +5,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 #include "../../include/ffb200.h"
 
 #define FFB_STR2(x) #x
@@ -36,6 +38,21 @@ void set_error(char const *fmt, ...);
       ffb::set_error(__VA_ARGS__);                                                          \
       return FFB_ERR_INVALID;                                                               \
     }                                                                                       \
+  } while (0)
+
+// cudaFuncSetAttribute acts on the CURRENT device only, and one host process may drive several GPUs from several
+// threads (the reference's Legion process model): a launch wrapper remembers, per call site, WHICH devices it has
+// configured.  Two threads racing here both set the same attribute - harmless.
+#define FFB_SET_MAX_SMEM_ONCE(kernel, bytes)                                                                  \
+  do {                                                                                                        \
+    static std::atomic<unsigned long long> _done{0};                                                          \
+    int _dev = 0;                                                                                             \
+    cudaGetDevice(&_dev);                                                                                     \
+    unsigned long long const _bit = (_dev >= 0 && _dev < 64) ? 1ULL << _dev : 0ULL;                           \
+    if (!(_done.load(std::memory_order_acquire) & _bit)) {                                                    \
+      FFB_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)));  \
+      _done.fetch_or(_bit, std::memory_order_release);                                                        \
+    }                                                                                                         \
   } while (0)
 
 constexpr int kNumSMs = 148; // B200: 2 dies x 74 SMs

@@ -195,7 +195,8 @@ linear_gemv_kernel(T const *__restrict__ A, T const *__restrict__ W, T const *__
         int const t = i >> 7, r = (i >> 3) & 15, c = i & 7;
         int const n0 = ((int)blockIdx.x + t * (int)gridDim.x) * GV_BN;
         if (r < M) {
-          float v = bias ? DT<T>::to_f(bias[n0 + c]) : 0.f;
+          // the reference adds the bias on EVERY shard before the sum (linear_kernels.cu:531, then allreduce): nranks x bias
+          float v = bias ? (float)pt.nranks * DT<T>::to_f(bias[n0 + c]) : 0.f;
           for (int p = 0; p < pt.nranks; p++) {
             float const *src = mine + 2 * (((size_t)p * kPeerMaxTokens + r) * pt.max_n + n0 + c);
             unsigned long long word;
@@ -236,11 +237,7 @@ static int launch_gemv_t(void const *in, void *out, void const *w, void const *b
   constexpr int K = KSTEPS * 16 * GV_CONSUMERS;
   constexpr int STAGE_BYTES = GV_BN * (K * 2 + 16);
   constexpr size_t smem = (size_t)(GV_RING_BYTES / STAGE_BYTES) * STAGE_BYTES + 2 * GV_CONSUMERS * 128 * 4;
-  static bool attr = false;
-  if (!attr) {
-    FFB_CUDA_TRY(cudaFuncSetAttribute(linear_gemv_kernel<T, KSTEPS, FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr = true;
-  }
+  FFB_SET_MAX_SMEM_ONCE((linear_gemv_kernel<T, KSTEPS, FUSED>), smem);
   int const ntiles = N / GV_BN;
   int const grid = ntiles < kNumSMs ? ntiles : kNumSMs;
   linear_gemv_kernel<T, KSTEPS, FUSED><<<grid, GV_THREADS, smem, s>>>((T const *)in, (T const *)w, (T const *)bias, (T *)out, M, N, pt);

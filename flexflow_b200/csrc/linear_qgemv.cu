@@ -329,11 +329,7 @@ int linear_qgemv_supported(int dtype, int quant, int M, int K, int N) {
 template <int QB, int SPT>
 static int launch_qgemv_t(void const *in, void *out, void const *w, void const *bias, int M, int N, cudaStream_t s) {
   constexpr size_t smem = QgCfg<QB>::SMEM;
-  static bool attr = false;
-  if (!attr) {
-    FFB_CUDA_TRY(cudaFuncSetAttribute(linear_qgemv_kernel<QB, SPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr = true;
-  }
+  FFB_SET_MAX_SMEM_ONCE((linear_qgemv_kernel<QB, SPT>), smem);
   int const ngroups = N / 32;
   int const grid = ngroups < kNumSMs ? ngroups : kNumSMs;
   linear_qgemv_kernel<QB, SPT><<<grid, QG_THREADS, smem, s>>>((__half const *)in, (uint8_t const *)w, (__half const *)bias,

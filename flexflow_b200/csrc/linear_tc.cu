@@ -134,17 +134,16 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static bool tried = false;
-  if (!tried) {
-    tried = true;
+  // function-local static: initialised once, thread-safe (C++11)
+  static EncodeTiledFn const fn = []() -> EncodeTiledFn {
     void *p = nullptr;
     cudaDriverEntryPointQueryResult q;
     if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
         q == cudaDriverEntryPointSuccess) {
-      fn = (EncodeTiledFn)p;
+      return (EncodeTiledFn)p;
     }
-  }
+    return nullptr;
+  }();
   return fn;
 }
 

@@ -409,11 +409,7 @@ int launch_one(void const *in, void *out, void const *w, void const *bias, int d
   if (rc != FFB_OK) {
     return rc;
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    FFB_CUDA_TRY(cudaFuncSetAttribute(linear_tc2_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(((size_t)225 << 10) + 1024)));
-    attr_set = true;
-  }
+  FFB_SET_MAX_SMEM_ONCE(linear_tc2_kernel<T>, ((size_t)225 << 10) + 1024);
   size_t const smem = (size_t)stages * stage + 16384 + 1024; // ring + epilogue staging + alignment slack
   int const tiles = ((N + BN - 1) / BN) * ((M + 255) / 256);
   dim3 grid(2 * std::min(tiles * S, kNumSMs / 2));

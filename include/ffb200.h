@@ -87,7 +87,11 @@ int ffb_attn_last_kernel_ms(ffb_attn_t h, float *ms_out);
  * packs the parts of the host batch descriptor the kernels need into a pinned staging block and
  * issues ONE cudaMemcpyAsync into the device mirror (the reference issues 2-6 pageable copies).
  * `bc_host` points at a BatchConfig / TreeVerifyBatchConfig / BeamSearchBatchConfig according
- * to `mode`.  `staging_pinned_host` must hold sizeof(ffb_combined_batch_config_meta) bytes. */
+ * to `mode`.  `staging_pinned_host` must hold sizeof(ffb_combined_batch_config_meta) bytes.
+ * Lifetime: the copy is asynchronous.  The call remembers, per (staging block, device), an event recorded behind the
+ * copy and waits for it before it writes the same block again, so a caller may reuse ONE staging block for every step
+ * however far its host thread runs ahead of the stream; bc_host itself is free again when the call returns.  The
+ * staging block must stay allocated until the stream has drained. */
 int ffb_load_batch_config(void const *bc_host, int mode, void *staging_pinned_host,
                           ffb_combined_batch_config_meta *meta_dev, ffb_stream_t stream);
 
@@ -179,7 +183,8 @@ int ffb_comm_has_peer(ffb_comm_t c);
  * back to back inside FusedOp::inference_task (src/ops/fused.cu:448-495; insertion rule src/runtime/model.cc:3421-3445).
  * Decode batches (<= 16 tokens) on a peer-mapped communicator run as ONE kernel that pushes the fp32 partial sums into
  * every rank's receive area and reduces them in rank order; otherwise ffb_linear_forward + ffb_allreduce.  Every
- * rank must make the same call. */
+ * rank must make the same call.  A bias is added on every shard before the sum, as in the reference (each shard's
+ * Linear adds it, linear_kernels.cu:531, then the AllReduce sums): the result carries nranks x bias on both paths. */
 int ffb_linear_forward_allreduce(ffb_linear_t h, ffb_comm_t comm, void const *in_dev, void *out_dev,
                                  void const *weight_dev, void const *bias_dev, int batch, ffb_stream_t stream);
 
