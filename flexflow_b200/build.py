@@ -28,6 +28,7 @@ SOURCES = [
     "norm_argmax.cu",
     "host_tree.cu",
     "request_manager.cu",
+    "weights_io.cu",
 ]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

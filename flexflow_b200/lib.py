@@ -93,6 +93,11 @@ SIGNATURES = {
     "ffb_rm_num_pending": (_i, [_vp]),
     "ffb_rm_num_processed_requests": (_sz, [_vp]),
     "ffb_fetch_inference_result": (_i, [_vp, _i, _vp, _vp]),
+    "ffb_load_from_file": (_i, [C.c_char_p, _vp, _sz, _i]),
+    "ffb_load_attention_weights_to_dense": (_i, [C.c_char_p, C.c_char_p, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "ffb_quantize_weights": (_i, [_vp, _i, _i, _i, _i, _vp]),
+    "ffb_save_quantized_file": (_i, [C.c_char_p, _vp, _i, _i, _i, _i]),
+    "ffb_load_from_quantized_file": (_i, [C.c_char_p, _i, _i, _sz, _vp]),
     "ffb_fetch_beam_inference_result": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
 }
 

@@ -316,6 +316,33 @@ int ffb_fetch_inference_result(int const *indices_dev, int num_tokens, ffb_infer
 int ffb_fetch_beam_inference_result(int const *indices_dev, float const *probs_dev, int num_tokens, int k,
                                     ffb_beam_inference_result *result_host, ffb_stream_t stream);
 
+/* ---- weight file formats and the quantiser (host code) ----------------------------------------------
+ * ffb_load_from_file: load_from_file (src/runtime/file_loader.cc:345-377): a flat binary of `count` elements of
+ * `dtype` (FFB_DT_HALF / FFB_DT_BF16 / FFB_DT_FLOAT); a short or missing file is FFB_ERR_INVALID (the reference
+ * asserts).
+ * ffb_load_attention_weights_to_dense: load_attention_weights_to_dense_v2 (file_loader.cc:215-343) for the dense layers
+ * either side of the attention operator.  load_o_proj == 0: reads `<layer_name>.q_proj.weight`, `.k_proj.weight`,
+ * `.v_proj.weight` ([heads * head_dim][hidden], HuggingFace order) and writes the column-parallel qkv_proj weight of
+ * shard `tp_rank`: [3 * (num_heads / tp) * head_dim][hidden] = [Q_r | K_r | V_r] with the kv heads replicated to q-head
+ * granularity (the layout ffb_*_attn_forward's input comes in).  load_o_proj != 0: reads `<layer_name>.o_proj.weight`
+ * ([hidden][num_heads * head_dim]) and writes the row-parallel shard [hidden][(num_heads / tp) * head_dim].
+ * tp_rank == -1 writes what the reference's function writes: all shards back to back (qkv) / the file as stored (o). */
+int ffb_load_from_file(char const *path, void *dst_host, size_t count, int dtype);
+int ffb_load_attention_weights_to_dense(char const *weights_folder, char const *layer_name, int dtype, int num_heads,
+                                        int num_kv_heads, int hidden_dim, int head_dim, int tp_degree, int tp_rank,
+                                        int load_o_proj, void *dst_host);
+/* The quantiser of inference/utils/compress_llama_weights.py:15-58 (num_bits 8 / 4, group_size 32, group_dim 0,
+ * asymmetric) on a [out_dim][in_dim] fp32 matrix: per (32-row group, column) min and scale = B / (max - min) in fp32,
+ * q = round_half_even(clamp((w - min) * scale, 0, B)); writes the blob [values | offsets | scales] (ffb_quant_blob_bytes
+ * bytes) with the group meta rounded to `dtype` (FFB_DT_HALF / FFB_DT_BF16).  A constant group gets q = 0 and an
+ * infinite scale, which dequantises to the constant (the script would produce NaN casts there). */
+int ffb_quantize_weights(float const *w_host, int in_dim, int out_dim, int quant_type, int dtype, void *blob_host);
+/* The three files FileDataLoader::load_quantization_weight reads for a non-attention tensor (file_loader.cc:552-669):
+ * `path` (ONE byte per element, 4-bit values included), `path`_offset, `path`_scale.  ffb_load_from_quantized_file is
+ * load_from_quantized_file: it fills the blob, packing two 4-bit values per byte, the first in the high nibble. */
+int ffb_save_quantized_file(char const *path, void const *blob_host, int in_dim, int out_dim, int quant_type, int dtype);
+int ffb_load_from_quantized_file(char const *path, int quant_type, int dtype, size_t blob_bytes, void *blob_host);
+
 #ifdef __cplusplus
 }
 #endif
