@@ -6,6 +6,8 @@
 //  src/ops/tree_inc_multihead_self_attention.cu:433-478; src/ops/spec_inc_multihead_self_attention.cu:311-358).
 // HBM-bound elementwise work: 128-bit loads/stores, sin/cos computed once per (token, pair)
 // instead of once per (token, head, pair).
+#include <cstdlib>
+
 #include "attn_state.h"
 
 namespace ffb {
@@ -223,7 +225,17 @@ static int launch_prep_t(ffb_attn_s *h, int mode, ffb_combined_batch_config_meta
   while (pb > 1 && (long)T_ * pb > 4L * kNumSMs) {
     pb = (pb + 1) / 2;
   }
+  // experiment hook: FFB_PREP_CARVEOUT=<percent> asks for that shared-memory carve-out, so that a small kernel between
+  // two 200 KB-shared-memory kernels does not flip the SMs' L1 / shared split twice
+  static int const carve = getenv("FFB_PREP_CARVEOUT") ? atoi(getenv("FFB_PREP_CARVEOUT")) : -1;
 #define FFB_PREP(DH)                                                                                   \
+  if (carve >= 0) {                                                                                    \
+    static bool set = false;                                                                           \
+    if (!set) {                                                                                        \
+      cudaFuncSetAttribute(prep_kernel<T, DH>, cudaFuncAttributePreferredSharedMemoryCarveout, carve); \
+      set = true;                                                                                      \
+    }                                                                                                  \
+  }                                                                                                    \
   prep_kernel<T, DH><<<dim3(T_, pb), 128, 0, s>>>((T const *)qkv, (T *)h->q_buf, (T *)h->k_cache, (T *)h->v_cache, \
                                         prev, h->qdesc, meta, mode, d.num_q_heads, d.num_kv_heads,     \
                                         h->cache_len, d.max_requests, rp, d.scaling_query,             \

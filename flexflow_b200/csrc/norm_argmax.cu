@@ -408,6 +408,110 @@ int launch_rms_norm(void const *x1, void const *x2, void const *w, void *res, vo
   return FFB_OK;
 }
 
+
+// Softmax over the last dimension (the op between lm_head and ArgMax / ArgTopK, inference/models/llama.cc:277-291; the
+// reference calls cudnnSoftmaxForward(ACCURATE, MODE_CHANNEL), src/ops/kernels/softmax.cu:262-288): one CTA per row,
+// the row is read ONCE from HBM (up to SM_REGS_ELEMS classes it stays in registers, longer rows are re-read from L2),
+// maximum and sum in fp32, exp through ex2, one rounding to DT at the end.
+constexpr int SM_THREADS = 1024, SM_VEC = 4; // 4 x 8 elements per thread in registers = 32768 classes
+template <typename T>
+__global__ void __launch_bounds__(SM_THREADS)
+softmax_kernel(T const *__restrict__ in, T *__restrict__ out, int V) {
+  int const row = blockIdx.x, tid = threadIdx.x;
+  T const *p = in + (size_t)row * V;
+  T *q = out + (size_t)row * V;
+  __shared__ float red[32];
+  __shared__ float bcast;
+  bool const vec_ok = ((size_t)row * V) % 8 == 0 && V % 8 == 0 && V <= SM_THREADS * SM_VEC * 8;
+  auto block_reduce = [&](float v, bool is_max) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      float const w = __shfl_xor_sync(0xffffffffu, v, o);
+      v = is_max ? fmaxf(v, w) : v + w;
+    }
+    if ((tid & 31) == 0) {
+      red[tid >> 5] = v;
+    }
+    __syncthreads();
+    if (tid < 32) {
+      float x = tid < (SM_THREADS >> 5) ? red[tid] : (is_max ? -INFINITY : 0.f);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        float const w = __shfl_xor_sync(0xffffffffu, x, o);
+        x = is_max ? fmaxf(x, w) : x + w;
+      }
+      if (tid == 0) {
+        bcast = x;
+      }
+    }
+    __syncthreads();
+    float const r = bcast;
+    __syncthreads();
+    return r;
+  };
+  constexpr float kLog2e = 1.4426950408889634f;
+  if (vec_ok) {
+    float f[SM_VEC][8];
+    int const nvec = V / 8;
+    float mx = -INFINITY;
+#pragma unroll
+    for (int u = 0; u < SM_VEC; u++) {
+      int const c = tid + u * SM_THREADS;
+      if (c < nvec) {
+        unpack8<T>(ldg_stream(p + (size_t)c * 8), f[u]);
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+          mx = fmaxf(mx, f[u][e]);
+        }
+      }
+    }
+    mx = block_reduce(mx, true);
+    float const base = mx == -INFINITY ? 0.f : mx * kLog2e;
+    float sum = 0.f;
+#pragma unroll
+    for (int u = 0; u < SM_VEC; u++) {
+      int const c = tid + u * SM_THREADS;
+      if (c < nvec) {
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+          f[u][e] = ffb_ex2(fmaf(f[u][e], kLog2e, -base));
+          sum += f[u][e];
+        }
+      }
+    }
+    sum = block_reduce(sum, false);
+    float const inv = 1.f / sum;
+#pragma unroll
+    for (int u = 0; u < SM_VEC; u++) {
+      int const c = tid + u * SM_THREADS;
+      if (c < nvec) {
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+          f[u][e] *= inv;
+        }
+        *reinterpret_cast<uint4 *>(q + (size_t)c * 8) = pack8<T>(f[u]);
+      }
+    }
+    return;
+  }
+  // long or unaligned rows: three passes (the second and third hit L2)
+  float mx = -INFINITY;
+  for (int i = tid; i < V; i += SM_THREADS) {
+    mx = fmaxf(mx, DT<T>::to_f(p[i]));
+  }
+  mx = block_reduce(mx, true);
+  float const base = mx == -INFINITY ? 0.f : mx * kLog2e;
+  float sum = 0.f;
+  for (int i = tid; i < V; i += SM_THREADS) {
+    sum += ffb_ex2(fmaf(DT<T>::to_f(p[i]), kLog2e, -base));
+  }
+  sum = block_reduce(sum, false);
+  float const inv = 1.f / sum;
+  for (int i = tid; i < V; i += SM_THREADS) {
+    q[i] = DT<T>::from_f(ffb_ex2(fmaf(DT<T>::to_f(p[i]), kLog2e, -base)) * inv);
+  }
+}
+
 } // namespace
 } // namespace ffb
 
@@ -456,6 +560,28 @@ int ffb_argmax(void const *input_dev, int *indices_dev, float *prob_dev, int *pa
   } else {
     argmax_kernel<__nv_bfloat16><<<num_tokens, threads, 0, (cudaStream_t)stream>>>(
         (__nv_bfloat16 const *)input_dev, indices_dev, prob_dev, parent_dev, length);
+  }
+  FFB_LAUNCH_CHECK();
+  return FFB_OK;
+}
+
+int ffb_softmax(void const *input_dev, void *output_dev, int num_tokens, int num_classes, int dtype, ffb_stream_t stream) {
+  using namespace ffb;
+  if (int rc = ffb_check_device()) {
+    return rc;
+  }
+  FFB_REQUIRE(input_dev && output_dev, "null argument");
+  FFB_REQUIRE(dtype == FFB_DT_HALF || dtype == FFB_DT_BF16, "dtype %d not supported", dtype);
+  FFB_REQUIRE(num_tokens >= 0 && num_classes > 0, "bad shape %d x %d", num_tokens, num_classes);
+  if (num_tokens == 0) {
+    return FFB_OK;
+  }
+  if (dtype == FFB_DT_HALF) {
+    softmax_kernel<__half><<<num_tokens, SM_THREADS, 0, (cudaStream_t)stream>>>((__half const *)input_dev, (__half *)output_dev,
+                                                                               num_classes);
+  } else {
+    softmax_kernel<__nv_bfloat16><<<num_tokens, SM_THREADS, 0, (cudaStream_t)stream>>>(
+        (__nv_bfloat16 const *)input_dev, (__nv_bfloat16 *)output_dev, num_classes);
   }
   FFB_LAUNCH_CHECK();
   return FFB_OK;

@@ -74,6 +74,7 @@ SIGNATURES = {
     "ffb_residual_rms_norm": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, C.c_float, _i, _vp]),
     "ffb_argmax": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
     "ffb_arg_topk": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "ffb_softmax": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "ffb_bitmask_init": (None, [_vp, _i]),
     "ffb_bitmask_update": (None, [_vp, _i, _i]),
     "ffb_bitmask_append_pending": (None, [_vp, _i]),

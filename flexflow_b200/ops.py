@@ -316,6 +316,23 @@ class RMSNorm:
                                                n, m.in_dim, m.eps, _dt_of(input), _stream()), "ffb_residual_rms_norm")
 
 
+class SoftmaxMeta:
+    """SoftmaxMeta (include/flexflow/ops/softmax.h): dim is always the class dimension on this path."""
+
+    def __init__(self, handler, dim=-1):
+        self.handle, self.dim = handler, dim
+
+
+class Softmax:
+    @staticmethod
+    def inference_kernel_wrapper(m, bc, is_last_op, input, output, output_grad=None):
+        """Kernels::Softmax::inference_kernel_wrapper (src/ops/kernels/softmax.cu:121-166): input / output
+        [num_tokens][num_classes] DT.  (output_grad, the PEFT copy of the last op, is outside the path.)"""
+        num_classes = input.shape[-1]
+        n = input.numel() // num_classes
+        L.check(L.load().ffb_softmax(_ptr(input), _ptr(output), n, num_classes, _dt_of(input), _stream()), "ffb_softmax")
+
+
 class ArgMaxMeta:
     """ArgMaxMeta (include/flexflow/ops/argmax.h): beam_search selects the prob / parent outputs."""
 

@@ -213,6 +213,11 @@ int ffb_argmax(void const *input_dev, int *indices_dev, float *prob_dev, int *pa
 int ffb_arg_topk(void const *input_dev, float *values_dev, int *indices_dev, int num_tokens, int length, int k,
                  int dtype, ffb_stream_t stream);
 
+/* Softmax::inference_kernel_wrapper (src/ops/kernels/softmax.cu:121-166,262-288; cudnnSoftmaxForward, ACCURATE, over the
+ * class dimension): output[t][c] = exp(input[t][c] - max_t) / sum_c, fp32 inside, one rounding to DT.  The op between
+ * lm_head and ArgMax / ArgTopK (inference/models/llama.cc:277-291).  In place (output_dev == input_dev) is allowed. */
+int ffb_softmax(void const *input_dev, void *output_dev, int num_tokens, int num_classes, int dtype, ffb_stream_t stream);
+
 /* ---- host-side SpecInfer tree logic (integer only; runs on the host, no CUDA call) ---------------------------------
  * The bit masks these build are what ffb_tree_attn_forward / ffb_spec_attn_forward read from causalMask[], and
  * ffb_traverse_verify_tree turns the LLM's per-node outputs into the accepted tokens and the commit list of the next

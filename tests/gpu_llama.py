@@ -106,7 +106,9 @@ class PathModel:
         if T == 0:
             return ir
         k = next(bc.beamRequestsInfo[i].beam_size for i in range(max_requests) if not bc.request_completed[i])
-        probs = torch.softmax(self.logits(bc), -1).to(self.dtype).contiguous()
+        lg = self.logits(bc).to(self.dtype).contiguous()
+        probs = torch.empty_like(lg)
+        ops.Softmax.inference_kernel_wrapper(ops.SoftmaxMeta(self.handler), bc, False, lg, probs)
         ops.ArgTopK.forward_kernel_wrapper(ops.ArgTopKMeta(self.handler, k, True), bc, probs, self.prob_buf[:T * k],
                                            self.idx_buf[:T * k], T)
         L.check(L.load().ffb_fetch_beam_inference_result(self.idx_buf.data_ptr(), self.prob_buf.data_ptr(), T, k,

@@ -224,3 +224,35 @@ def test_arg_topk_equals_the_reference_kernel(shape, k):
     torch.cuda.synchronize()
     assert torch.equal(idx, want_idx), (idx[:2], want_idx[:2])
     assert torch.equal(probs[:, :k - 1], want_val[:, :k - 1])
+
+
+@pytest.mark.parametrize("dt", ["half", "bf16"])
+@pytest.mark.parametrize("rows,classes", [(16, 32000), (512, 32000), (3, 128256), (5, 1003), (2, 8), (7, 32768)])
+def test_softmax_matches_fp32_reference(dt, rows, classes):
+    """ffb_softmax (Softmax::inference_kernel_wrapper, the op between lm_head and the token selection): against an fp32
+    softmax of the same 16-bit inputs - every probability within one rounding of DT (+ a 2e-6 floor for the ex2 / divide
+    approximations), rows sum to 1, the argmax survives, in-place operation allowed."""
+    import torch
+    from flexflow_b200 import ops
+    tdt = torch.float16 if dt == "half" else torch.bfloat16
+    g = torch.Generator(device="cuda").manual_seed(rows * 7 + classes)
+    x = (torch.randn(rows, classes, generator=g, device="cuda") * 3.0).to(tdt)
+    if rows > 2:
+        x[1] = -1e4 if dt == "half" else -1e30     # a flat row
+        x[2, classes // 2] = 60.0                  # one dominant class
+    y = torch.empty_like(x)
+    ops.Softmax.inference_kernel_wrapper(ops.SoftmaxMeta(None), None, False, x, y)
+    torch.cuda.synchronize()
+    want = torch.softmax(x.float(), -1)
+    eps = 2.0 ** -11 if dt == "half" else 2.0 ** -8
+    err = (y.float() - want).abs()
+    tol = want * (2 * eps) + (6e-8 if dt == "half" else 1e-30) + 2e-6 * want
+    assert bool((err <= tol + 1e-7).all()), float((err - tol).max())
+    assert bool(((y.float().sum(-1) - 1).abs() < 2e-2).all())
+    top = want.max(-1)
+    clear = top.values > want.topk(2, -1).values[:, 1] * (1 + 8 * eps)
+    assert bool((y.float().argmax(-1)[clear] == top.indices[clear]).all())
+    z = x.clone()
+    ops.Softmax.inference_kernel_wrapper(ops.SoftmaxMeta(None), None, False, z, z)
+    torch.cuda.synchronize()
+    assert torch.equal(z, y)
