@@ -74,13 +74,25 @@ prep_kernel(T const *__restrict__ qkv, T *__restrict__ q_buf, T *__restrict__ k_
     }
   }
   bool const pos_ok = slot_ok && cache_pos >= 0 && cache_pos < cache_len;
-  if (threadIdx.x == 0 && blockIdx.y == 0) {
-    QueryDesc qd;
-    qd.slot = slot_ok ? slot : 0;
-    qd.kv_len = slot_ok ? max(0, min(kv_len, cache_len)) : 0;
-    qd.ntcs = ntcs;
-    qd.bit = (bit >= 0 && bit < 64) ? bit : (bit < 0 ? -1 : 64); // 64: nothing beyond ntcs visible
-    qdesc[t] = qd;
+  if (threadIdx.x < 32 && blockIdx.y == 0) {
+    // warp 0 transposes the query's column of the request's tree mask: lane i holds mask[i] and mask[i + 32]
+    unsigned long long vis = 0ULL;
+    if (bit >= 0 && bit < 64 && slot_ok) { // (uniform across the warp)
+      unsigned long long const m0 = meta->causalMask[slot].mask[threadIdx.x];
+      unsigned long long const m1 = meta->causalMask[slot].mask[threadIdx.x + 32];
+      uint32_t const lo = __ballot_sync(0xffffffffu, (m0 >> bit) & 1ULL);
+      uint32_t const hi = __ballot_sync(0xffffffffu, (m1 >> bit) & 1ULL);
+      vis = ((unsigned long long)hi << 32) | lo;
+    }
+    if (threadIdx.x == 0) {
+      QueryDesc qd;
+      qd.slot = slot_ok ? slot : 0;
+      qd.kv_len = slot_ok ? max(0, min(kv_len, cache_len)) : 0;
+      qd.ntcs = ntcs;
+      qd.bit = (bit >= 0 && bit < 64) ? bit : (bit < 0 ? -1 : 64); // 64: nothing beyond ntcs visible
+      qd.vis = vis;
+      qdesc[t] = qd;
+    }
   }
 
   // sin/cos of this token's position, once per complex pair (reference: per head and pair)

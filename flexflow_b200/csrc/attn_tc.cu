@@ -15,11 +15,16 @@
 //   warp 9 (one lane)  MMA issuer: S = Q K^T (UMMA 128x128x16, Q from TENSOR MEMORY, K from smem K-major) into one
 //                      of two TMEM score buffers, then O += P V (P from tensor memory - it overwrites the first
 //                      64 columns of its own score buffer - and V consumed MN-major exactly as TMA laid it down)
-//   warps 0-7          two threads per query row (warps w and w+4 share TMEM lane quarter w, each takes 64 of
-//                      the 128 keys and half of the output columns): tcgen05.ld the scores, scale + kv_len /
-//                      causal / tree-bit mask, online softmax in the log2 domain against a LAZY reference
-//                      maximum (the TMEM accumulator is rescaled only when a row maximum grows by more than
-//                      2^8, so P stays <= 256 and most tiles need no correction), P back into TMEM (tcgen05.st)
+//   warps 0-15         FOUR threads per query row (warps w, w+4, w+8, w+12 share TMEM lane quarter w % 4; each takes
+//                      32 of the 128 keys and a quarter of the output columns): tcgen05.ld the scores, scale + kv_len /
+//                      causal / tree-bit mask, online softmax in the log2 domain against a LAZY reference maximum (the
+//                      TMEM accumulator is rescaled only when a row maximum grows by more than 2^8, so P stays <= 256
+//                      and most tiles need no correction), P back into TMEM (tcgen05.st).  A 64-token MHA tree fills
+//                      only 64 of a unit's 128 rows, i.e. lane quarters 0 and 1: with two threads per row four of
+//                      eight warps did all the work at 64 elements each and the tile loop ran at 1.2 us per tile,
+//                      bound by their issue rate and exposed tcgen05.ld / st latency (phase trace, profiles/); with
+//                      four threads per row eight warps share it at 32 elements each.
+// The tree mask of a query row arrives TRANSPOSED in its QueryDesc (one word per row, written by the prep kernel).
 // Shared memory holds nothing but the K/V stream.  HBM-bound: 64 KB of K/V per tile per SM
 // (~2900 cycles at the HBM rate) against ~1000 tensor-pipe and ~1000 MUFU cycles.
 #include <algorithm>
@@ -35,7 +40,11 @@ using namespace tc;
 
 namespace {
 
-constexpr int TBM = 128, TBN = 128, ATC_SOFTMAX_THREADS = 256, ATC_THREADS = 320;
+constexpr int TBM = 128, TBN = 128;
+constexpr int ATC_NQ = 4;                               // threads per query row = column quarters of a key tile
+constexpr int ATC_SOFTMAX_THREADS = TBM * ATC_NQ;       // warps 0 .. 4 NQ - 1
+constexpr int ATC_PRODUCER_WARP = 4 * ATC_NQ, ATC_MMA_WARP = 4 * ATC_NQ + 1;
+constexpr int ATC_THREADS = ATC_SOFTMAX_THREADS + 64;
 constexpr float kRescaleThreshold = 8.f; // log2 domain
 constexpr int ATC_MAX_ENT = 128;
 
@@ -62,8 +71,10 @@ template <int DH> struct AtcCfg {
   static constexpr uint32_t HALF_BYTES = 128 * 128;     // one [128 keys][64 cols] swizzled block
   static constexpr uint32_t KV_BYTES = KH * HALF_BYTES; // one K tile or one V tile
   static constexpr int NBUF = (160 * 1024) / KV_BYTES;  // ring slots; K and V tiles alternate: K0 V0 K1 V1 ...
-  static constexpr uint32_t Q_BYTES = 128 * DH * 2;      // next segment's Q rows, staged by cp.async
-  static constexpr size_t SMEM = (size_t)NBUF * KV_BYTES + Q_BYTES + 16384 + 1024; // ring + Q + output staging + alignment
+  // next segment's Q rows, staged by cp.async as [softmax warp][lane][DH / 2 bytes]; the same per-warp blocks serve as
+  // the output staging tiles of the epilogue (Q has been moved to tensor memory by then)
+  static constexpr uint32_t Q_BYTES = 128 * DH * 2;
+  static constexpr size_t SMEM = (size_t)NBUF * KV_BYTES + Q_BYTES + 1024; // ring + Q / output staging + alignment
 };
 
 // Walks the segments of one CTA: maximal runs of consecutive flattened tiles inside one unit.
@@ -95,7 +106,7 @@ struct SegWalk {
 };
 
 template <typename T, int DH>
-// 10 warps are allocated as 12 (warp allocation granularity 4): 65536 / 384 = 170 registers per thread at most
+// 18 warps are allocated as 20 (warp allocation granularity 4): 65536 / 640 = 102 registers per thread at most
 __global__ void __launch_bounds__(ATC_THREADS, 1)
 attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
                const __grid_constant__ AtcSched sched_param, T const *__restrict__ q_buf,
@@ -108,11 +119,9 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t kv_full[NBUF], kv_empty[NBUF];
   __shared__ __align__(8) uint64_t s_full[2], o_full, p_full, q_full;
-  __shared__ float s_xch[2][2][TBM]; // [tile parity][column half][row]: partial row maxima / final row sums
+  __shared__ float s_xch[2][ATC_NQ][TBM]; // [tile parity][column quarter][row]: partial row maxima / final row sums
   __shared__ uint32_t tmem_base_smem;
   __shared__ int s_rowlast[TBM];
-  // tree bit masks of the current / next segment's request, TRANSPOSED: bit i of s_maskT[.][b] = bit b of mask[i]
-  __shared__ unsigned long long s_maskT[2][64];
   __shared__ AtcSched s_sched;
 
   int const tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -144,8 +153,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
 #endif
   // 128B-swizzled operand blocks need 1024-byte alignment
   uint8_t *sKV = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-  uint8_t *const sQ = sKV + (size_t)NBUF * Cfg::KV_BYTES;     // [128 rows][DH] of the NEXT segment's Q
-  uint8_t *const sStage = sQ + Cfg::Q_BYTES;                  // 8 softmax warps x 2 KB output staging
+  uint8_t *const sQ = sKV + (size_t)NBUF * Cfg::KV_BYTES;     // the NEXT segment's Q / this segment's output staging
 
   // The tile schedule is walked by all three roles at every unit boundary.  In parameter (constant) space each
   // first touch of a line is a ~0.7 us miss and the walks are dependent chains (2 us per boundary, measured): copy
@@ -161,7 +169,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
   __syncthreads();
   AtcSched const &sched = s_sched;
 
-  if (warp == 8) {
+  if (warp == ATC_PRODUCER_WARP) {
     // ===== TMA producer =====  (never waits for the rest of the CTA: the stream starts at once)
     if (lane == 0) {
       for (int sb = 0; sb < NBUF; sb++) {
@@ -201,7 +209,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
       }
     }
   } else {
-    if (warp == 9) {
+    if (warp == ATC_MMA_WARP) {
       // TMEM: score buffers S0 S1 (P overwrites the first 64 columns of its S), output accumulator, Q operand
       asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "r"(512u));
       asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
@@ -212,7 +220,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
     uint32_t const tmem_base = tmem_base_smem;
     uint32_t const tmem_S = tmem_base, tmem_O = tmem_base + 256, tmem_Q = tmem_base + 384;
 
-    if (warp == 9) {
+    if (warp == ATC_MMA_WARP) {
       if (lane == 0) {
         // ===== MMA issuer =====
         // cute::UMMA::InstrDescriptor: c_format F32 (1) @4, a/b format @7/@10 (F16 0, BF16 1), b_major @16
@@ -276,84 +284,65 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
         }
       }
     } else {
-      // ===== softmax warps: threads (row, h) with h = warp / 4 own keys [64h, 64h+64) of every tile =====
+      // ===== softmax warps: thread (row, hc) owns keys [32 hc, 32 hc + 32) of every tile and DH / 4 output columns =====
       int const row = tid & (TBM - 1), hc = tid >> 7;
       uint32_t const lane_sel = (uint32_t)((warp & 3) * 32) << 16;
-      uint32_t const pair_bar = 1 + (warp & 3); // named barrier shared by warps w and w+4
-      constexpr int OC = DH / 2;                // output columns per thread
-      constexpr int QW = DH / 4;                // 32-bit words of Q per thread (half a row)
+      uint32_t const quad_bar = 1 + (warp & 3); // named barrier shared by the NQ warps of one lane quarter
+      constexpr int KC = TBN / ATC_NQ;          // keys (score columns) per thread: 32
+      constexpr int PC = KC / 2;                // packed P columns per thread: 16
+      constexpr int OC = DH / ATC_NQ;           // output columns per thread: 32 (Dh 128) / 16 (Dh 64)
+      constexpr int QW = DH / 2 / ATC_NQ;       // 32-bit words of Q per thread: 16 / 8
+      constexpr int QCH = QW / 4;               // 16-byte chunks of this thread's Q / output slice: 4 / 2
+      static_assert(KC == 32 && (OC == 32 || OC == 16), "tile shape");
       uint32_t const tO = tmem_O + lane_sel + (uint32_t)(hc * OC);
       uint32_t const tq = tmem_Q + lane_sel + (uint32_t)(hc * QW);
+      // this warp's 32 x (DH / 2)-byte block of the Q / staging area; 16-byte chunks XOR-swizzled by lane so that both the
+      // thread-per-row accesses and the 4 (2)-lanes-per-row read-back of the epilogue are conflict-free
+      uint8_t *const wblk = sQ + (size_t)warp * (32 * QCH * 16);
+      int const swz = QCH == 4 ? ((lane >> 1) & 3) : ((lane >> 2) & 1);
 
       // Row data of a segment: fetched one segment ahead (global loads in flight during the tile loop), so a unit
       // boundary costs no exposed global-memory latency.
       int n_th = -1, n_kvl = 0, n_bit = -1;
-      unsigned long long n_mask = 0;
+      unsigned long long n_vis = 0;
       auto fetch_rows = [&](SegWalk const &sw) {
         AtcEntry const &en = sched.ent[sw.e];
         int const R = en.mt * TBM + row;
         n_th = -1;
         n_kvl = 0;
         n_bit = -1;
+        n_vis = 0;
         if (R < en.qlen * G) {
           int const tok = en.first_tok + R / G;
           n_th = tok * nq + sw.kvh * G + R % G;
           QueryDesc const qd = qdesc[tok];
           n_kvl = qd.kv_len;
           n_bit = qd.bit;
-          // this thread's half row of Q -> shared memory, asynchronously (no registers held while the current
-          // segment streams; under load an L2 round trip at the unit boundary costs 2-3 us).  16-byte units are
-          // XOR-swizzled by row so that the read-back at publish time is conflict-free.
-          uint32_t const dst = smem_u32(sQ) + (uint32_t)row * (DH * 2) + (uint32_t)hc * DH;
-          T const *src = q_buf + (size_t)n_th * DH + hc * (DH / 2);
+          n_vis = qd.vis;
+          // this thread's quarter row of Q -> shared memory, asynchronously (no registers held while the current
+          // segment streams; under load an L2 round trip at the unit boundary costs 2-3 us)
+          uint32_t const dst = smem_u32(wblk) + (uint32_t)lane * (QCH * 16);
+          T const *src = q_buf + (size_t)n_th * DH + hc * (DH / ATC_NQ);
 #pragma unroll
-          for (int c = 0; c < QW / 4; c++) {
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + (uint32_t)((c ^ (row & (QW / 4 - 1))) << 4)),
-                         "l"(src + c * 8) : "memory");
+          for (int c = 0; c < QCH; c++) {
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + (uint32_t)((c ^ swz) << 4)), "l"(src + c * 8) : "memory");
           }
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
-        if (hc == 1 && row < 64) {
-          n_mask = meta->causalMask[en.slot].mask[row];
-        }
       };
-      // Q -> tensor memory (all QK^T MMAs of the previous segment have completed: their s_full phases were observed),
-      // row tables -> shared-memory buffer `tb`
-      auto publish_rows = [&](int tb) {
-        uint32_t n_q[32];
+      // Q -> tensor memory (all QK^T MMAs of the previous segment have completed: their s_full phases were observed)
+      auto publish_rows = [&]() {
+        uint32_t n_q[QW];
         asm volatile("cp.async.wait_group 0;" ::: "memory");
-        uint8_t const *src = sQ + (size_t)row * (DH * 2) + hc * DH;
+        uint8_t const *src = wblk + (size_t)lane * (QCH * 16);
 #pragma unroll
-        for (int c = 0; c < QW / 4; c++) {
-          uint4 const v = n_th >= 0 ? *reinterpret_cast<uint4 const *>(src + ((c ^ (row & (QW / 4 - 1))) << 4))
-                                    : make_uint4(0u, 0u, 0u, 0u);
+        for (int c = 0; c < QCH; c++) {
+          uint4 const v = n_th >= 0 ? *reinterpret_cast<uint4 const *>(src + ((c ^ swz) << 4)) : make_uint4(0u, 0u, 0u, 0u);
           n_q[c * 4 + 0] = v.x; n_q[c * 4 + 1] = v.y; n_q[c * 4 + 2] = v.z; n_q[c * 4 + 3] = v.w;
         }
-        if (DH == 128) {
-          tmem_st32(tq, n_q);
-        } else {
-          tmem_st16(tq, n_q);
-        }
+        tmem_stN<QW>(tq, n_q);
         tmem_st_wait();
-        if (hc == 1 && row < 64) {
-          // warps 4 and 5 hold mask[0..31] / mask[32..63], one word per lane: 64 ballots transpose them (lane l keeps
-          // the words of bits l and l + 32); the two warps write the low / high halves of the transposed words
-          uint32_t keep0 = 0, keep1 = 0;
-#pragma unroll 8
-          for (int bb = 0; bb < 32; bb++) {
-            uint32_t const b0 = __ballot_sync(0xffffffffu, (n_mask >> bb) & 1ULL);
-            uint32_t const b1 = __ballot_sync(0xffffffffu, (n_mask >> (bb + 32)) & 1ULL);
-            if ((row & 31) == bb) {
-              keep0 = b0;
-              keep1 = b1;
-            }
-          }
-          uint32_t *const dstw = reinterpret_cast<uint32_t *>(&s_maskT[tb][0]) + (row >> 5);
-          dstw[2 * (row & 31)] = keep0;
-          dstw[2 * ((row & 31) + 32)] = keep1;
-        }
-        // (release) the first QK^T of the segment is issued after all 256 arrivals, and every softmax thread reads
-        // s_maskT[tb] only after that MMA's s_full: no CTA-wide barrier at the unit boundary
+        // (release) the first QK^T of the segment is issued after all arrivals: no CTA-wide barrier at the unit boundary
         tc_fence_before();
         mbar_arrive(&q_full);
       };
@@ -361,12 +350,12 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
       SegWalk w;
       w.init(sched);
       bool have = w.next(sched);
-      int g0 = 0, tb = 0;
+      int g0 = 0;
       if (tid == 0) FFB_TR(2, 100);
       if (have) {
         fetch_rows(w);
         if (tid == 0) FFB_TR(2, 101);
-        publish_rows(0);
+        publish_rows();
       }
       if (tid == 0) FFB_TR(2, 102);
       while (have) {
@@ -377,6 +366,9 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
         int const c_first = U0 / sched.rg, npieces = (U0 + en.ntiles - 1) / sched.rg - c_first + 1;
         int const piece = (int)blockIdx.x - c_first;
         int const th = n_th, kvl = n_kvl, bit = n_bit;
+        // tree / beam rows: bit i of row_vis says whether tree position i (key ntcs + i) is visible to this row
+        // (mask rule tree_…cu:165-169 / spec_…cu:165-167 with 1ULL semantics), transposed by the prep kernel
+        unsigned long long const row_vis = n_vis;
         bool const warp_active = __any_sync(0xffffffffu, th >= 0); // padding-only warps just keep the barriers moving
         if (tid == 0) FFB_TR(2, 105);
         have = w.next(sched);
@@ -386,61 +378,50 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
         }
         if (tid == 0) FFB_TR(2, 104);
         float m_ref = -INFINITY, l = 0.f;
-        // tree / beam rows: bit i of row_vis says whether tree position i (key ntcs + i) is visible to this row
-        // (mask rule tree_…cu:165-169 / spec_…cu:165-167 with 1ULL semantics), transposed once per segment
-        unsigned long long row_vis = 0;
 
         for (int it = 0; it < ntiles; it++) {
           int const g = g0 + it, b = g & 1;
-          int const kbase = (t_first + it) * TBN + hc * 64; // first key of this thread's 64 columns
+          int const kbase = (t_first + it) * TBN + hc * KC; // first key of this thread's columns
           uint32_t const tS = tmem_S + (uint32_t)b * 128u + lane_sel;
-          bool const need_mask = __any_sync(0xffffffffu, th >= 0 && (kbase + 64 > kvl || (bit >= 0 && kbase + 64 > ntcs)));
-          float sc[64];
+          bool const need_mask = __any_sync(0xffffffffu, th >= 0 && (kbase + KC > kvl || (bit >= 0 && kbase + KC > ntcs)));
+          float sc[KC];
           if (tid == 0) FFB_TR(2, 1000 + g);
           mbar_wait(&s_full[b], (g >> 1) & 1);
           if (tid == 0) FFB_TR(2, 2000 + g);
           tc_fence_after();
-          if (it == 0 && bit >= 0 && bit < 64) {
-            row_vis = s_maskT[tb][bit];
-          }
           float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
           if (warp_active) {
-            uint32_t r0[32], r1[32];
-            tmem_ld32_nowait(tS + (uint32_t)(hc * 64), r0);
-            tmem_ld32_nowait(tS + (uint32_t)(hc * 64 + 32), r1);
-            tmem_ld_wait();
+            uint32_t r0[32];
+            tmem_ld32(tS + (uint32_t)(hc * KC), r0);
 #pragma unroll
             for (int e = 0; e < 32; e++) { // raw scores; the (positive) scale is folded into the exponent below
               sc[e] = __uint_as_float(r0[e]);
-              sc[32 + e] = __uint_as_float(r1[e]);
             }
             if (need_mask) {
-              // visibility of this thread's 64 keys as one 64-bit word: kv_len / causal bound, then the tree bits
+              // visibility of this thread's 32 keys as one word: kv_len / causal bound, then the tree bits
               int const lim = kvl - kbase;
-              unsigned long long V = lim >= 64 ? ~0ULL : (lim <= 0 ? 0ULL : ((1ULL << lim) - 1ULL));
+              uint32_t V = lim >= 32 ? ~0u : (lim <= 0 ? 0u : ((1u << lim) - 1u));
               if (bit >= 0) {
                 int const off = kbase - ntcs; // tree position of column 0
-                unsigned long long tv;
+                uint32_t tv;
                 if (off >= 64) {
-                  tv = 0ULL;
+                  tv = 0u;
                 } else if (off >= 0) {
-                  tv = row_vis >> off;
-                } else if (off > -64) {
-                  tv = (row_vis << (-off)) | ((1ULL << (-off)) - 1ULL);
+                  tv = (uint32_t)(row_vis >> off);
+                } else if (off > -32) {
+                  tv = (uint32_t)((row_vis << (-off)) | ((1ULL << (-off)) - 1ULL));
                 } else {
-                  tv = ~0ULL;
+                  tv = ~0u;
                 }
                 V &= tv;
               }
-              uint32_t const vlo = (uint32_t)V, vhi = (uint32_t)(V >> 32);
 #pragma unroll
               for (int e = 0; e < 32; e++) {
-                sc[e] = (vlo >> e) & 1u ? sc[e] : -INFINITY;
-                sc[32 + e] = (vhi >> e) & 1u ? sc[32 + e] : -INFINITY;
+                sc[e] = (V >> e) & 1u ? sc[e] : -INFINITY;
               }
             }
 #pragma unroll
-            for (int e = 0; e < 64; e += 4) {
+            for (int e = 0; e < KC; e += 4) {
               mx0 = fmaxf(mx0, sc[e]);
               mx1 = fmaxf(mx1, sc[e + 1]);
               mx2 = fmaxf(mx2, sc[e + 2]);
@@ -449,8 +430,11 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
           }
           float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * scale_log2; // log2 domain from here on
           s_xch[b][hc][row] = mx;
-          asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
-          mx = fmaxf(mx, s_xch[b][hc ^ 1][row]);
+          asm volatile("bar.sync %0, %1;" ::"r"(quad_bar), "n"(32 * ATC_NQ) : "memory");
+#pragma unroll
+          for (int o = 1; o < ATC_NQ; o++) {
+            mx = fmaxf(mx, s_xch[b][(hc + o) & (ATC_NQ - 1)][row]);
+          }
           // lazy reference maximum: move it (and rescale the accumulator) only when the row maximum outgrows it by 2^8
           bool const grow = mx > m_ref + kRescaleThreshold || (m_ref == -INFINITY && mx > -INFINITY);
           float const alpha = grow ? (m_ref == -INFINITY ? 1.f : ffb_ex2(m_ref - mx)) : 1.f;
@@ -463,25 +447,22 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
             // (the MMA of this tile cannot start before this thread arrives on p_full)
             mbar_wait(&o_full, (g - 1) & 1);
             tc_fence_after();
+            uint32_t r[OC];
+            tmem_ldN<OC>(tO, r);
 #pragma unroll
-            for (int c = 0; c < OC / 32; c++) {
-              uint32_t r[32];
-              tmem_ld32(tO + (uint32_t)(c * 32), r);
-#pragma unroll
-              for (int e = 0; e < 32; e++) {
-                r[e] = __float_as_uint(__uint_as_float(r[e]) * alpha);
-              }
-              tmem_st32(tO + (uint32_t)(c * 32), r);
+            for (int e = 0; e < OC; e++) {
+              r[e] = __float_as_uint(__uint_as_float(r[e]) * alpha);
             }
+            tmem_stN<OC>(tO, r);
             tmem_st_wait();
           }
           if (warp_active) {
-            // P (16-bit pairs) overwrites the first 64 columns of this tile's score buffer: this thread's 64 keys are
-            // columns [32h, 32h+32); the partner finished reading its scores before the pair barrier above
+            // P (16-bit pairs) overwrites the first 64 columns of this tile's score buffer: this thread's 32 keys are
+            // columns [16 hc, 16 hc + 16); every thread of the row finished reading its scores before the barrier above
             float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-            uint32_t pk[32];
+            uint32_t pk[PC];
 #pragma unroll
-            for (int e = 0; e < 64; e += 4) {
+            for (int e = 0; e < KC; e += 4) {
               float f0 = fmaf(sc[e], scale_log2, -base), f1 = fmaf(sc[e + 1], scale_log2, -base);
               float f2 = fmaf(sc[e + 2], scale_log2, -base), f3 = fmaf(sc[e + 3], scale_log2, -base);
               f0 = ffb_ex2(f0);
@@ -496,8 +477,10 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
               pk[e / 2 + 1] = DT<T>::pack(f2, f3);
             }
             l = l * alpha + ((s0 + s1) + (s2 + s3));
-            tmem_st32(tS + (uint32_t)(hc * 32), pk);
+            tmem_stN<PC>(tS + (uint32_t)(hc * PC), pk);
             tmem_st_wait();
+          } else {
+            l = l * alpha;
           }
           if (g > 0) {
             // Phase bookkeeping: every thread observes every o_full phase in order, and cannot arrive on p_full for
@@ -511,50 +494,61 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
         // The next segment's Q goes to tensor memory BEFORE this segment's epilogue, so its first QK^T MMAs run
         // while the output of this one is read out (its first PV MMA waits for these threads' p_full anyway).
         if (have) {
-          publish_rows(tb ^ 1);
+          publish_rows();
         }
-        // ---- segment epilogue: row sum over both column halves, then output or split record ----
+        // ---- segment epilogue: row sum over the column quarters, then output or split record ----
         int const g_last = g0 + ntiles - 1;
         if (tid == 0) FFB_TR(2, 4000);
         s_xch[0][hc][row] = l;
         mbar_wait(&o_full, g_last & 1);
         if (tid == 0) FFB_TR(2, 4010);
         tc_fence_after();
-        asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+        asm volatile("bar.sync %0, %1;" ::"r"(quad_bar), "n"(32 * ATC_NQ) : "memory");
         if (tid == 0) FFB_TR(2, 4020);
-        l += s_xch[0][hc ^ 1][row];
+        l = 0.f;
+#pragma unroll
+        for (int o = 0; o < ATC_NQ; o++) { // the same order in every thread of the row: one value of l per row
+          l += s_xch[0][o][row];
+        }
+        // registers -> this warp's staging tile (thread per row) -> global with QCH lanes per row, so that a warp
+        // store covers 32 / QCH rows x (DH / 2) contiguous bytes (a thread-per-row store touches 32 lines per
+        // instruction: LSU-bound).  `f` holds this thread's OC output values.
+        auto store_row_slice = [&](float const (&f)[OC]) {
+          uint8_t *const mine = wblk + (size_t)lane * (QCH * 16);
+#pragma unroll
+          for (int c = 0; c < QCH; c++) {
+            float v8[8];
+#pragma unroll
+            for (int e = 0; e < 8; e++) {
+              v8[e] = f[c * 8 + e];
+            }
+            *reinterpret_cast<uint4 *>(mine + ((c ^ swz) << 4)) = pack8<T>(v8);
+          }
+          __syncwarp();
+          constexpr int RPI = 32 / QCH; // rows per store instruction
+#pragma unroll
+          for (int i = 0; i < QCH; i++) {
+            int const rr = i * RPI + lane / QCH, j = lane % QCH;
+            int const rswz = QCH == 4 ? ((rr >> 1) & 3) : ((rr >> 2) & 1);
+            uint4 const v = *reinterpret_cast<uint4 const *>(wblk + (size_t)rr * (QCH * 16) + ((j ^ rswz) << 4));
+            int const thr = __shfl_sync(0xffffffffu, th, rr);
+            if (thr >= 0) {
+              *reinterpret_cast<uint4 *>(out + (size_t)thr * DH + hc * OC + j * 8) = v;
+            }
+          }
+          __syncwarp();
+        };
         if (npieces == 1) {
           if (warp_active) {
-            // TMEM -> registers (x 1/sum, convert) -> this warp's 32 x 64 B staging tile (16-byte units XOR-swizzled
-            // by row pair: conflict-free both ways) -> global with 4 lanes per row, so that a warp store covers
-            // 8 rows x 64 contiguous bytes (a thread-per-row store touches 32 lines per instruction: LSU-bound)
             float const inv = __fdividef(1.f, l + 1.e-6f);
-            uint8_t *const stg = sStage + warp * 2048;
+            uint32_t r[OC];
+            tmem_ldN<OC>(tO, r);
+            float f[OC];
 #pragma unroll
-            for (int c = 0; c < OC / 32; c++) {
-              uint32_t r[32];
-              tmem_ld32(tO + (uint32_t)(c * 32), r);
-#pragma unroll
-              for (int v4 = 0; v4 < 4; v4++) {
-                float f[8];
-#pragma unroll
-                for (int e = 0; e < 8; e++) {
-                  f[e] = __uint_as_float(r[v4 * 8 + e]) * inv;
-                }
-                *reinterpret_cast<uint4 *>(stg + lane * 64 + ((v4 ^ ((lane >> 1) & 3)) << 4)) = pack8<T>(f);
-              }
-              __syncwarp();
-#pragma unroll
-              for (int i = 0; i < 4; i++) {
-                int const rr = i * 8 + (lane >> 2), j = lane & 3;
-                uint4 const v = *reinterpret_cast<uint4 const *>(stg + rr * 64 + ((j ^ ((rr >> 1) & 3)) << 4));
-                int const thr = __shfl_sync(0xffffffffu, th, rr);
-                if (thr >= 0) {
-                  *reinterpret_cast<uint4 *>(out + (size_t)thr * DH + hc * OC + c * 32 + j * 8) = v;
-                }
-              }
-              __syncwarp();
+            for (int e = 0; e < OC; e++) {
+              f[e] = __uint_as_float(r[e]) * inv;
             }
+            store_row_slice(f);
           }
         } else {
           // Split records live in per-CTA slots laid out [DH + 2][128 rows] (column-major over the rows), so that a
@@ -580,7 +574,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
               }
               s_rowlast[row] = f;
             }
-            asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+            asm volatile("bar.sync %0, %1;" ::"r"(quad_bar), "n"(32 * ATC_NQ) : "memory");
             mode = s_rowlast[row];
           }
           if (mode != 0 && warp_active) {
@@ -602,49 +596,48 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
             L += l * wa;
             L += lb * wb;
             float const inv = __fdividef(1.f, L + 1.e-6f);
-            uint4 *dst = reinterpret_cast<uint4 *>(out + (size_t)(th >= 0 ? th : 0) * DH + hc * OC);
+            uint32_t r[OC];
+            tmem_ldN<OC>(tO, r);
+            float f[OC];
 #pragma unroll
-            for (int c = 0; c < OC / 32; c++) {
-              uint32_t r[32];
-              tmem_ld32(tO + (uint32_t)(c * 32), r);
-              if (mode == 2) {
+            for (int e = 0; e < OC; e++) {
+              f[e] = fmaf(__uint_as_float(r[e]), wa, fmaf(vb[e], wb, 0.f)) * inv;
+            }
+            if (mode == 2) {
+              uint4 *dst = reinterpret_cast<uint4 *>(out + (size_t)th * DH + hc * OC);
 #pragma unroll
-                for (int v4 = 0; v4 < 4; v4++) {
-                  float f[8];
+              for (int c = 0; c < QCH; c++) {
+                float v8[8];
 #pragma unroll
-                  for (int e = 0; e < 8; e++) {
-                    f[e] = fmaf(__uint_as_float(r[v4 * 8 + e]), wa, fmaf(vb[c * 32 + v4 * 8 + e], wb, 0.f)) * inv;
-                  }
-                  dst[c * 4 + v4] = pack8<T>(f);
+                for (int e = 0; e < 8; e++) {
+                  v8[e] = f[c * 8 + e];
                 }
+                dst[c] = pack8<T>(v8);
               }
             }
           }
           if (mode == 0 && warp_active) {
             float *rec = partial + (size_t)(2 * (int)blockIdx.x + (piece < npieces - 1 ? 1 : 0)) * SLOT + row;
+            uint32_t r[OC];
+            tmem_ldN<OC>(tO, r);
 #pragma unroll
-            for (int c = 0; c < OC / 32; c++) {
-              uint32_t r[32];
-              tmem_ld32(tO + (uint32_t)(c * 32), r);
-#pragma unroll
-              for (int e = 0; e < 32; e++) {
-                rec[(hc * OC + c * 32 + e) * TBM] = __uint_as_float(r[e]);
-              }
+            for (int e = 0; e < OC; e++) {
+              rec[(hc * OC + e) * TBM] = __uint_as_float(r[e]);
             }
             if (hc == 0) {
               rec[DH * TBM] = m_ref;
               rec[(DH + 1) * TBM] = l;
             }
           }
-          // per-row arrival counters: the last piece to finish a (token, head) row merges the records; both threads
-          // of the row merge their own half of the columns (exact log-sum-exp merge, then the reference's
+          // per-row arrival counters: the last piece to finish a (token, head) row merges the records; every thread
+          // of the row merges its own quarter of the columns (exact log-sum-exp merge, then the reference's
           // 1/(sum + 1e-6), inc_…cu:538)
           if (tid == 0) FFB_TR(2, 4100);
           if (mode == 0) {
             __threadfence();
           }
           if (tid == 0) FFB_TR(2, 4200);
-          asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+          asm volatile("bar.sync %0, %1;" ::"r"(quad_bar), "n"(32 * ATC_NQ) : "memory");
           if (hc == 0 && mode == 0) {
             int last = 0;
             if (th >= 0) {
@@ -656,7 +649,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
             }
             s_rowlast[row] = last;
           }
-          asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+          asm volatile("bar.sync %0, %1;" ::"r"(quad_bar), "n"(32 * ATC_NQ) : "memory");
           if (tid == 0) FFB_TR(2, 4300 + s_rowlast[row]);
           if (mode == 0 && s_rowlast[row]) {
             __threadfence();
@@ -672,49 +665,43 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
             }
             float const inv = __fdividef(1.f, L + 1.e-6f);
             uint4 *dst = reinterpret_cast<uint4 *>(out + (size_t)th * DH + hc * OC);
-            // 32 columns x 2 pieces per batch: 64 independent loads in flight per thread
+            float acc[OC];
+#pragma unroll
+            for (int d = 0; d < OC; d++) {
+              acc[d] = 0.f;
+            }
+            // OC columns x 2 pieces per batch: up to 64 independent loads in flight per thread
 #pragma unroll 1
-            for (int c = 0; c < OC / 32; c++) {
-              float acc[32];
+            for (int i = 0; i < npieces; i += 2) {
+              bool const two = i + 1 < npieces;
+              float const *ra = slot_of(i), *rb = slot_of(two ? i + 1 : i);
+              float const ma = __ldcg(ra + DH * TBM), mb = __ldcg(rb + DH * TBM);
+              float va[OC], vb[OC];
 #pragma unroll
-              for (int d = 0; d < 32; d++) {
-                acc[d] = 0.f;
+              for (int d = 0; d < OC; d++) {
+                va[d] = __ldcg(ra + (hc * OC + d) * TBM);
+                vb[d] = __ldcg(rb + (hc * OC + d) * TBM);
               }
-#pragma unroll 1
-              for (int i = 0; i < npieces; i += 2) {
-                bool const two = i + 1 < npieces;
-                float const *ra = slot_of(i), *rb = slot_of(two ? i + 1 : i);
-                float const ma = __ldcg(ra + DH * TBM), mb = __ldcg(rb + DH * TBM);
-                float va[32], vb[32];
+              float const wa = ma == -INFINITY ? 0.f : ffb_ex2(ma - M);
+              float const wb = (!two || mb == -INFINITY) ? 0.f : ffb_ex2(mb - M);
 #pragma unroll
-                for (int d = 0; d < 32; d++) {
-                  va[d] = __ldcg(ra + (hc * OC + c * 32 + d) * TBM);
-                  vb[d] = __ldcg(rb + (hc * OC + c * 32 + d) * TBM);
-                }
-                float const wa = ma == -INFINITY ? 0.f : ffb_ex2(ma - M);
-                float const wb = (!two || mb == -INFINITY) ? 0.f : ffb_ex2(mb - M);
-#pragma unroll
-                for (int d = 0; d < 32; d++) {
-                  acc[d] = fmaf(va[d], wa, fmaf(vb[d], wb, acc[d]));
-                }
+              for (int d = 0; d < OC; d++) {
+                acc[d] = fmaf(va[d], wa, fmaf(vb[d], wb, acc[d]));
               }
+            }
 #pragma unroll
-              for (int v4 = 0; v4 < 4; v4++) {
-                float f[8];
+            for (int c = 0; c < QCH; c++) {
+              float v8[8];
 #pragma unroll
-                for (int e = 0; e < 8; e++) {
-                  f[e] = acc[v4 * 8 + e] * inv;
-                }
-                dst[c * 4 + v4] = pack8<T>(f);
+              for (int e = 0; e < 8; e++) {
+                v8[e] = acc[c * 8 + e] * inv;
               }
+              dst[c] = pack8<T>(v8);
             }
             if (tid == 0) FFB_TR(2, 4400);
           }
         }
         if (tid == 0) FFB_TR(2, 5000);
-        // (s_maskT is double-buffered: buffer tb is rewritten at the end of the NEXT segment, by which time every
-        // warp - none can run a tile ahead of the p_full / o_full handshakes - has read it)
-        tb ^= 1;
         g0 += ntiles;
       }
       tc_fence_before();
@@ -722,7 +709,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 9) {
+  if (warp == ATC_MMA_WARP) {
     tc_fence_after();
     __syncwarp();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base_smem), "r"(512u));

@@ -119,6 +119,9 @@ struct QueryDesc {
   int kv_len;
   int ntcs;
   int bit;
+  // the query's row of the tree mask, TRANSPOSED by the prep kernel: bit i set <=> tree position i (key ntcs + i) is
+  // visible to this query, i.e. bit `bit` of causalMask[slot].mask[i] (0 when bit is outside [0, 64))
+  unsigned long long vis;
 };
 
 __device__ __forceinline__ float ffb_ex2(float x) {

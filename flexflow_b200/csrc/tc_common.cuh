@@ -146,6 +146,26 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, uint32_t const (&r)[32
         "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
       : "memory");
 }
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, uint32_t const (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, uint32_t const (&r)[8]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+               ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
+// N consecutive fp32 columns of this warp's 32 lanes <-> registers (N = 8, 16 or 32); the load waits for completion
+template <int N> __device__ __forceinline__ void tmem_ldN(uint32_t taddr, uint32_t (&r)[N]);
+template <> __device__ __forceinline__ void tmem_ldN<32>(uint32_t taddr, uint32_t (&r)[32]) { tmem_ld32(taddr, r); }
+template <> __device__ __forceinline__ void tmem_ldN<16>(uint32_t taddr, uint32_t (&r)[16]) { tmem_ld16(taddr, r); }
+template <int N> __device__ __forceinline__ void tmem_stN(uint32_t taddr, uint32_t const (&r)[N]);
+template <> __device__ __forceinline__ void tmem_stN<32>(uint32_t taddr, uint32_t const (&r)[32]) { tmem_st32(taddr, r); }
+template <> __device__ __forceinline__ void tmem_stN<16>(uint32_t taddr, uint32_t const (&r)[16]) { tmem_st16(taddr, r); }
+template <> __device__ __forceinline__ void tmem_stN<8>(uint32_t taddr, uint32_t const (&r)[8]) { tmem_st8(taddr, r); }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 } // namespace tc

@@ -11,6 +11,7 @@
 #pragma once
 #include <stdexcept>
 #include <string>
+#include <vector>
 
 #include "../../include/ffb200.h"
 
@@ -209,6 +210,119 @@ struct ArgTopK {
     check(ffb_arg_topk(input.ptr, speculative_decoding ? probs : nullptr, indices, batch_size, length, k, input.data_type,
                        stream), "ffb_arg_topk");
   }
+};
+
+// Softmax::inference_kernel_wrapper (src/ops/kernels/softmax.cu:121-166)
+struct Softmax {
+  static void inference_kernel_wrapper(ffb_batch_config const *bc, GenericTensorAccessorR const &input,
+                                       GenericTensorAccessorW const &output, int num_classes, ffb_stream_t stream) {
+    check(ffb_softmax(input.ptr, output.ptr, bc->num_tokens, num_classes, input.data_type, stream), "ffb_softmax");
+  }
+};
+
+// The D2H that ends a model step (ArgMax::inference_task, src/ops/argmax.cc:300-372)
+inline void fetch_inference_result(int const *indices_dev, int num_tokens, ffb_inference_result *ir, ffb_stream_t stream) {
+  check(ffb_fetch_inference_result(indices_dev, num_tokens, ir, stream), "ffb_fetch_inference_result");
+}
+
+// RequestManager (include/flexflow/request_manager.h:117-357): configuration, request registration and the batch
+// builders, with the reference's method names; the serving loops are the callers' (see host/incr_decoding.cc).
+class RequestManager {
+public:
+  void set_max_requests_per_batch(int n) { d_.max_requests_per_batch = n; }
+  void set_max_tokens_per_batch(int n) { d_.max_tokens_per_batch = n; }
+  void set_max_spec_tree_token_num(int n) { d_.max_spec_tree_token_num = n; }
+  void set_max_sequence_length(int n) { d_.max_sequence_length = n; }
+  int get_max_requests_per_batch() const { return d_.max_requests_per_batch; }
+  int get_max_tokens_per_batch() const { return d_.max_tokens_per_batch; }
+  int get_max_verify_tokens_per_batch() const {
+    return d_.max_tokens_per_batch + d_.max_spec_tree_token_num * d_.max_requests_per_batch;
+  }
+  int register_ssm_model() { return d_.num_ssms++; }
+  void push_spec_infer_tree_width(int w) { widths_.push_back(w); }
+  void register_tokenizer(std::vector<int> const &eos_token_ids) {
+    d_.num_eos_tokens = 0;
+    for (int e : eos_token_ids) {
+      if (d_.num_eos_tokens < 8) {
+        d_.eos_token_ids[d_.num_eos_tokens++] = e;
+      }
+    }
+  }
+  ~RequestManager() { ffb_rm_destroy(h_); }
+  RequestManager() = default;
+  RequestManager(RequestManager const &) = delete;
+  RequestManager &operator=(RequestManager const &) = delete;
+
+  size_t register_new_request(std::vector<int> const &prompt_tokens, int max_length = -1, int max_new_tokens = -1) {
+    size_t guid = 0;
+    check(ffb_rm_register_request(handle(), prompt_tokens.data(), (int)prompt_tokens.size(), max_length, max_new_tokens, &guid),
+          "ffb_rm_register_request");
+    return guid;
+  }
+  void prepare_next_batch(ffb_batch_config const &old_bc, ffb_inference_result const &result, ffb_batch_config *new_bc) {
+    check(ffb_rm_prepare_next_batch(handle(), &old_bc, &result, new_bc), "ffb_rm_prepare_next_batch");
+  }
+  void prepare_next_batch_init(ffb_tree_verify_batch_config const &old_bc, ffb_inference_result const &result, int model_id,
+                               ffb_beam_search_batch_config *new_bc) {
+    check(ffb_rm_prepare_next_batch_init(handle(), &old_bc, &result, model_id, new_bc), "ffb_rm_prepare_next_batch_init");
+  }
+  void prepare_next_batch_beam(ffb_beam_search_batch_config const &old_bc, ffb_beam_inference_result const &result,
+                               ffb_beam_search_batch_config *new_bc) {
+    check(ffb_rm_prepare_next_batch_beam(handle(), &old_bc, &result, new_bc), "ffb_rm_prepare_next_batch_beam");
+  }
+  void prepare_next_batch_verify(std::vector<ffb_beam_search_batch_config const *> const &old_batches,
+                                 ffb_tree_verify_batch_config *new_bc) {
+    check(ffb_rm_prepare_next_batch_verify(handle(), old_batches.data(), (int)old_batches.size(), new_bc),
+          "ffb_rm_prepare_next_batch_verify");
+  }
+  std::vector<int> request_tokens(size_t guid) {
+    int n = 0;
+    check(ffb_rm_request_tokens(handle(), guid, nullptr, 0, &n), "ffb_rm_request_tokens");
+    std::vector<int> t((size_t)n);
+    check(ffb_rm_request_tokens(handle(), guid, t.data(), n, &n), "ffb_rm_request_tokens");
+    return t;
+  }
+  int num_pending() { return ffb_rm_num_pending(handle()); }
+  size_t get_num_processed_requests() { return ffb_rm_num_processed_requests(handle()); }
+
+private:
+  ffb_rm_t handle() {
+    if (!h_) {
+      check(ffb_rm_create(&d_, &h_), "ffb_rm_create");
+      for (int w : widths_) {
+        check(ffb_rm_push_spec_infer_tree_width(h_, w), "ffb_rm_push_spec_infer_tree_width");
+      }
+    }
+    return h_;
+  }
+  ffb_rm_desc d_{};
+  std::vector<int> widths_;
+  ffb_rm_t h_ = nullptr;
+};
+
+// FileDataLoader (include/flexflow/utils/file_loader.h, src/runtime/file_loader.cc) for the layers of the path
+class FileDataLoader {
+public:
+  FileDataLoader(std::string weights_folder, int num_heads, int num_kv_heads, int hidden_dim, int qkv_inner_dim,
+                 int tensor_parallelism_degree, int data_type)
+      : folder_(std::move(weights_folder)), nh_(num_heads), nkv_(num_kv_heads), hidden_(hidden_dim), dh_(qkv_inner_dim),
+        tp_(tensor_parallelism_degree), dt_(data_type) {}
+  // qkv_proj ([3 * H_l][hidden]) or o_proj ([hidden][H_l]) weight of one TP shard into host memory
+  void load_attention_weights_to_dense(std::string const &layer_name, bool load_o_proj, int tp_rank, void *dst_host) const {
+    check(ffb_load_attention_weights_to_dense(folder_.c_str(), layer_name.c_str(), dt_, nh_, nkv_, hidden_, dh_, tp_, tp_rank,
+                                              load_o_proj, dst_host), "ffb_load_attention_weights_to_dense");
+  }
+  void load_from_file(std::string const &name, void *dst_host, size_t count) const {
+    check(ffb_load_from_file((folder_ + "/" + name).c_str(), dst_host, count, dt_), "ffb_load_from_file");
+  }
+  void load_from_quantized_file(std::string const &name, int quantization_type, size_t blob_bytes, void *blob_host) const {
+    check(ffb_load_from_quantized_file((folder_ + "/" + name).c_str(), quantization_type, dt_, blob_bytes, blob_host),
+          "ffb_load_from_quantized_file");
+  }
+
+private:
+  std::string folder_;
+  int nh_, nkv_, hidden_, dh_, tp_, dt_;
 };
 
 } // namespace ffb
