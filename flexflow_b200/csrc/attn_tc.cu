@@ -807,9 +807,28 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
     }
     return worst;
   };
+  // A unit cut into three or more pieces takes the general (record + counter + last-arriver) merge, a dependent chain
+  // of L2 round trips: one more penalty per extra piece.  The search runs up to the longest unit, so that a batch
+  // with fewer units than SMs (head-sharded shards: 32 units of 9 tiles at TP = 8) runs one whole unit per CTA
+  // instead of cutting every unit to fill all SMs (measured 39 us -> see profiles/).
+  int max_nt = 1;
+  for (int i = 0; i < sc.n_ent; i++) {
+    max_nt = std::max(max_nt, (int)sc.ent[i].ntiles);
+  }
+  auto max_pieces = [&](int rgc) {
+    int worst = 1;
+    for (int i = 0; i < sc.n_ent; i++) {
+      for (int hh = 0; hh < d.num_kv_heads; hh++) {
+        int const u0 = sc.ent[i].cum + hh * sc.ent[i].ntiles, u1 = u0 + sc.ent[i].ntiles - 1;
+        worst = std::max(worst, u1 / rgc - u0 / rgc + 1);
+      }
+    }
+    return worst;
+  };
   int rg = rg0, best_cost = 1 << 30;
-  for (int rgc = rg0; rgc <= 2 * rg0; rgc++) {
-    int const cost = rgc + 4 * max_partials(rgc);
+  int const rg_hi = std::max(2 * rg0, max_nt), step = std::max(1, (rg_hi - rg0) / 96);
+  for (int rgc = rg0; rgc <= rg_hi; rgc += step) {
+    int const cost = rgc + 4 * max_partials(rgc) + 4 * std::max(0, max_pieces(rgc) - 2);
     if (cost < best_cost) {
       best_cost = cost;
       rg = rgc;
