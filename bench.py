@@ -418,7 +418,9 @@ def tp_parity(W):
     wo = gather(o_l.weight)        # shard r: columns of its heads (file_loader.cc:350-354)
     kf, vf = gather(W.kfill), gather(W.vfill)
     res = {"ranks_bit_identical": bool(identical),
-           "path": ("fused o_proj + NVLink peer-push allreduce" if (W.kind == "decode" and D.comm.has_peer) else "o_proj + ncclAllReduce")}
+           "path": ("o_proj + ncclAllReduce" if not D.comm.has_peer else
+                    ("fused o_proj + NVLink peer-push allreduce (one kernel)" if W.kind == "decode" else
+                     "o_proj GEMM + two-shot peer-memory allreduce kernel (reduce-scatter / all-gather by NVLink push)"))}
     err = torch.zeros(1, device=D.dev, dtype=torch.float64)
     if D.rank == 0:
         H_l = W.H_l

@@ -25,6 +25,7 @@ SOURCES = [
     "linear_tc2.cu",
     "capi_linear.cu",
     "comm.cu",
+    "peer_allreduce.cu",
     "norm_argmax.cu",
     "host_tree.cu",
     "request_manager.cu",

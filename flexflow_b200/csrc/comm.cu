@@ -100,7 +100,12 @@ void peer_setup(ffb_comm_s *c, NcclApi *api) {
   }
   size_t const recv_bytes = (size_t)2 * c->nranks * kPeerMaxTokens * kPeerMaxN * 2 * sizeof(float); // {value, epoch}
   size_t const flag_bytes = (size_t)c->nranks * kPeerMaxCtas * sizeof(int);
-  size_t const total = recv_bytes + flag_bytes + 256;
+  // large-message area: per rank 2 parities x 2 phases x one whole message, + its flags
+  size_t const small_bytes = (recv_bytes + flag_bytes + 256 + 1023) & ~(size_t)1023;
+  size_t const big_slice = ((kPeerBigMaxBytes / c->nranks + 1023) & ~(size_t)1023);
+  size_t const big_bytes = (size_t)4 * c->nranks * big_slice;
+  size_t const big_flag_bytes = ((size_t)2 * c->nranks * kPeerBigChunks * sizeof(int) + 256 + 1023) & ~(size_t)1023;
+  size_t const total = small_bytes + big_flag_bytes + big_bytes;
   struct Rec {
     cudaIpcMemHandle_t handle;
     int ok;
@@ -137,6 +142,8 @@ void peer_setup(ffb_comm_s *c, NcclApi *api) {
     }
     c->peer.recv[r] = (float *)base;
     c->peer.flags[r] = (int *)((char *)base + recv_bytes);
+    c->peer.big_flags[r] = (int *)((char *)base + small_bytes);
+    c->peer.big[r] = (char *)base + small_bytes + big_flag_bytes;
   }
   // second agreement: did EVERY rank map every area?
   int flag = ok ? 1 : 0;
@@ -154,6 +161,9 @@ void peer_setup(ffb_comm_s *c, NcclApi *api) {
   c->peer.max_n = kPeerMaxN;
   c->peer.epoch = (int *)((char *)c->peer_local + recv_bytes + flag_bytes);
   c->peer.done = c->peer.epoch + 1;
+  c->peer.big_slice_bytes = big_slice;
+  c->peer.big_epoch = (int *)((char *)c->peer_local + small_bytes + (size_t)2 * c->nranks * kPeerBigChunks * sizeof(int));
+  c->peer.big_done = c->peer.big_epoch + 1;
   c->peer_ok = true;
 }
 
@@ -238,6 +248,13 @@ int ffb_allreduce(ffb_comm_t c, void const *in, void *out, size_t count, int dty
   }
   int const nt = dtype == FFB_DT_HALF ? ncclFloat16 : (dtype == FFB_DT_BF16 ? ncclBfloat16 : (dtype == FFB_DT_FLOAT ? ncclFloat32 : -1));
   FFB_REQUIRE(nt >= 0, "dtype %d not supported by allreduce", dtype);
+  // messages up to 16 MiB on a peer-mapped communicator: two-shot allreduce over NVLink peer memory (peer_allreduce.cu);
+  // FFB_DISABLE_PEER_ALLREDUCE=1 keeps the NCCL call (A/B, parity tests).  Every rank must take the same branch: the
+  // condition depends only on values that are equal on all ranks (count, dtype, the agreed peer_ok) and this variable.
+  static bool const peer_off = getenv("FFB_DISABLE_PEER_ALLREDUCE") != nullptr;
+  if (!peer_off && c->peer_ok && ffb::peer_allreduce_supported(&c->peer, count, dtype)) {
+    return ffb::launch_peer_allreduce(&c->peer, in, out, count, dtype, (cudaStream_t)stream);
+  }
   NcclApi *api = nccl();
   if (!api) {
     return FFB_ERR_NCCL;

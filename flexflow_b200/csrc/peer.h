@@ -21,7 +21,18 @@ struct PeerTable {
   int *flags[kPeerMaxRanks];
   int *epoch; // local: number of fused collectives completed on this communicator
   int *done;  // local: CTA completion counter of the collective in flight
+  // ---- large messages (peer_allreduce.cu): two-shot allreduce, reduce-scatter then all-gather, both by PUSH ----
+  // big[p]: rank p's area [2 (epoch parity)][2 (0 = reduce-scatter, 1 = all-gather)][nranks (source)][big_slice_bytes];
+  // big_flags[p]: rank p's [2 (phase)][nranks (source)][kPeerBigChunks] ints holding the epoch of the last chunk that
+  // has landed (epochs only grow)
+  char *big[kPeerMaxRanks];
+  int *big_flags[kPeerMaxRanks];
+  size_t big_slice_bytes = 0;
+  int *big_epoch; // local
+  int *big_done;  // local
 };
+constexpr int kPeerBigChunks = 128;                        // CTAs (= flag slots per source) of the large-message kernel
+constexpr size_t kPeerBigMaxBytes = (size_t)16 << 20;      // largest message: 1024 tokens x 8192 x 2 bytes
 
 } // namespace ffb
 
@@ -30,4 +41,7 @@ struct ffb_comm_s;
 namespace ffb {
 // nullptr when the communicator has no peer mapping (single rank, IPC unavailable, adopted ncclComm_t)
 PeerTable const *comm_peer_table(ffb_comm_s *c);
+// two-shot allreduce of `count` 16-bit elements over peer memory (peer_allreduce.cu); in-place allowed
+int peer_allreduce_supported(PeerTable const *pt, size_t count, int dtype);
+int launch_peer_allreduce(PeerTable const *pt, void const *in, void *out, size_t count, int dtype, cudaStream_t s);
 } // namespace ffb

@@ -93,8 +93,33 @@ def main():
             assert all(torch.equal(gathered[0], t) for t in gathered), "ranks disagree on the fused result"
         os.environ.pop("FFB_DISABLE_FUSED_ALLREDUCE", None)
         assert worst < 5e-3, worst
+        # large messages: the two-shot peer-memory allreduce kernel (peer_allreduce.cu) behind ffb_allreduce.  The
+        # result must be the fp32 sum of the ranks' 16-bit inputs in RANK ORDER rounded once - bit for bit, on every
+        # rank, in place and out of place, over many back-to-back collectives (epoch parity, flag reuse) and sizes
+        # (whole slices, ragged last slice / chunk, the 16 MiB maximum).
+        import ctypes as C
+        from flexflow_b200 import batch_config as B
+        from flexflow_b200 import lib as L
+        sizes = [8, 4096, 12 * 1024, 512 * 4096, 1000 * 1000, 8 * 1024 * 1024, 64 * 4096 + 8]
+        for it in range(30):
+            n = sizes[it % len(sizes)]
+            dt = torch.float16 if it % 2 == 0 else torch.bfloat16
+            xin = (torch.randn(n, generator=g) * 2).to(dt).to(dev) * (rank + 1)
+            parts = [torch.empty_like(xin) for _ in range(world)]
+            dist.all_gather(parts, xin)
+            want = parts[0].float()
+            for t in parts[1:]:
+                want = want + t.float()
+            want = want.to(dt)
+            y = xin.clone() if it % 3 == 0 else torch.empty_like(xin)
+            src = y if it % 3 == 0 else xin
+            st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+            L.check(L.load().ffb_allreduce(comm._h, C.c_void_p(src.data_ptr()), C.c_void_p(y.data_ptr()), n,
+                                           B.DT_HALF if dt == torch.float16 else B.DT_BF16, st), "ffb_allreduce")
+            torch.cuda.synchronize()
+            assert torch.equal(y.view(torch.int16), want.view(torch.int16)), "peer allreduce differs (n=%d, it=%d)" % (n, it)
         if rank == 0:
-            print("PEER_OK worst %.2e" % worst)
+            print("PEER_OK worst %.2e, large-message allreduce bit-exact" % worst)
     dist.barrier()
     if rank == 0:
         print("TP_OK")
