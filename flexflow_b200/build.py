@@ -23,6 +23,7 @@ SOURCES = [
     "linear_qgemv.cu",
     "linear_tc.cu",
     "linear_tc2.cu",
+    "linear_tc4.cu",
     "capi_linear.cu",
     "comm.cu",
     "peer_allreduce.cu",

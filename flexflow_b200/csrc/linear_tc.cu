@@ -172,6 +172,9 @@ int make_tensor_map_2d(CUtensorMap *tm, int dtype, void const *ptr, long rows, i
 
 
 int linear_tc2_supported(int dtype, int M, int K, int N);
+// linear_tc4.cu: the same SM-pair tiles in clusters of two pairs sharing A by TMA multicast (FFB_TC4=1)
+int linear_tc4_supported(int dtype, int M, int K, int N);
+int launch_linear_tc4(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N, cudaStream_t s);
 int launch_linear_tc2(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N,
                       void *ws, int *cnt, cudaStream_t s);
 size_t linear_tc2_ws_bytes();
@@ -250,6 +253,9 @@ int launch_linear_tc(LinearTcState *st, int dtype, int quant, void const *in, vo
     wd = st->scratch;
   }
   // M > 128 (or an N the 128-wide 1-SM tiles do not divide): SM-pair tiles (linear_tc2.cu)
+  if (M > 128 && linear_tc4_supported(dtype, M, K, N)) {
+    return launch_linear_tc4(dtype, in, out, wd, bias, M, K, N, s);
+  }
   if ((M > 128 || N % 128 != 0) && linear_tc2_supported(dtype, M, K, N)) {
     return launch_linear_tc2(dtype, in, out, wd, bias, M, K, N, st->splitk_ws, st->splitk_cnt, s);
   }
