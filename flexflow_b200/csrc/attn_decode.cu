@@ -227,7 +227,7 @@ int choose_chunk(ffb_attn_s *h, long units, int kv_len_max, int granule, long ta
       break;
     }
   }
-  if (char const *e = getenv(env_name)) {
+  if (char const *e = ffb::env(env_name)) {
     int v = atoi(e);
     if (v > 0) {
       chunk = v;
@@ -248,7 +248,7 @@ int launch_decode_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta
   if (T <= 0) {
     return FFB_OK;
   }
-  int const U = getenv("FFB_DECODE_U") ? atoi(getenv("FFB_DECODE_U")) : 8; // keys per warp-load group
+  int const U = ffb::env("FFB_DECODE_U") ? atoi(ffb::env("FFB_DECODE_U")) : 8; // keys per warp-load group
   int const granule = kDecodeWarps * 8 * (32 / (d.head_dim / 8));
   int nsplit = 1;
   int chunk = choose_chunk(h, (long)T * d.num_q_heads, kv_len_max < 1 ? 1 : kv_len_max, granule,
@@ -261,7 +261,7 @@ int launch_decode_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta
   }
   float const scale = d.qk_prod_scaling ? 1.0f / sqrtf((float)d.head_dim) : 1.0f;
   float const scale_log2 = scale * 1.4426950408889634f;
-  int const fuse = getenv("FFB_SEPARATE_COMBINE") ? 0 : 1;
+  int const fuse = ffb::env("FFB_SEPARATE_COMBINE") ? 0 : 1;
   dim3 grid(nsplit, d.num_q_heads, T);
   if (h->profiling) {
     cudaEventRecord(h->ev0, s);

@@ -421,7 +421,7 @@ int launch_multi_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta,
   }
   float const scale = d.qk_prod_scaling ? 1.0f / sqrtf((float)d.head_dim) : 1.0f;
   float const scale_log2 = scale * 1.4426950408889634f;
-  int const fuse = getenv("FFB_SEPARATE_COMBINE") ? 0 : 1;
+  int const fuse = ffb::env("FFB_SEPARATE_COMBINE") ? 0 : 1;
   dim3 grid(nsplit, d.num_kv_heads * m_tiles, d.max_requests);
   if (h->profiling) {
     cudaEventRecord(h->ev0, s);

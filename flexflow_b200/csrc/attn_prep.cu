@@ -239,7 +239,7 @@ static int launch_prep_t(ffb_attn_s *h, int mode, ffb_combined_batch_config_meta
   }
   // experiment hook: FFB_PREP_CARVEOUT=<percent> asks for that shared-memory carve-out, so that a small kernel between
   // two 200 KB-shared-memory kernels does not flip the SMs' L1 / shared split twice
-  static int const carve = getenv("FFB_PREP_CARVEOUT") ? atoi(getenv("FFB_PREP_CARVEOUT")) : -1;
+  static int const carve = ffb::env("FFB_PREP_CARVEOUT") ? atoi(ffb::env("FFB_PREP_CARVEOUT")) : -1;
 #define FFB_PREP(DH)                                                                                   \
   if (carve >= 0) {                                                                                    \
     static bool set = false;                                                                           \

@@ -726,7 +726,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
 } // namespace
 
 int attn_tc_supported(ffb_attn_s *h) {
-  return h->tm_ready && !getenv("FFB_DISABLE_ATTN_TC");
+  return h->tm_ready && !ffb::env("FFB_DISABLE_ATTN_TC");
 }
 
 int attn_tc_init(ffb_attn_s *h) {
@@ -834,7 +834,7 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
       rg = rgc;
     }
   }
-  if (char const *e = getenv("FFB_ATC_RG")) {
+  if (char const *e = ffb::env("FFB_ATC_RG")) {
     int v = atoi(e);
     if (v > 0) {
       rg = v;
@@ -856,7 +856,7 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
   float const scale_log2 = scale * 1.4426950408889634f;
   static long long *trace = nullptr;
   static int trace_calls = 0;
-  bool const tracing = getenv("FFB_ATC_TRACE") != nullptr;
+  bool const tracing = ffb::env("FFB_ATC_TRACE") != nullptr;
   if (tracing && !trace) {
     cudaMalloc(&trace, (3 * 512 + 3 * 160) * sizeof(long long));
   }
@@ -886,7 +886,7 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
     cudaEventRecord(h->ev1, s);
   }
   FFB_LAUNCH_CHECK();
-  if (tracing && ++trace_calls == atoi(getenv("FFB_ATC_TRACE"))) { // dump the n-th launch
+  if (tracing && ++trace_calls == atoi(ffb::env("FFB_ATC_TRACE"))) { // dump the n-th launch
     static long long host[3 * 512 + 3 * 160];
     cudaStreamSynchronize(s);
     cudaMemcpy(host, trace, sizeof(host), cudaMemcpyDeviceToHost);

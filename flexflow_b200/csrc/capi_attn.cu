@@ -22,11 +22,48 @@ void set_error(char const *fmt, ...) {
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
 }
+namespace {
+struct EnvSlot {
+  std::atomic<char const *> key{nullptr};
+  std::atomic<char const *> val{nullptr};
+  std::atomic<int> gen{-1};
+};
+constexpr int kEnvSlots = 256;
+EnvSlot g_env[kEnvSlots];
+std::atomic<int> g_env_gen{0};
+} // namespace
+
+char const *env(char const *name) {
+  int const gen = g_env_gen.load(std::memory_order_acquire);
+  size_t const h0 = ((uintptr_t)name >> 2) % kEnvSlots;
+  for (int i = 0; i < kEnvSlots; i++) {
+    EnvSlot &sl = g_env[(h0 + i) % kEnvSlots];
+    char const *k = sl.key.load(std::memory_order_acquire);
+    if (k == nullptr) {
+      char const *expected = nullptr;
+      if (!sl.key.compare_exchange_strong(expected, name, std::memory_order_acq_rel) && expected != name) {
+        continue; // another thread claimed the slot for a different name
+      }
+      k = name;
+    }
+    if (k == name) {
+      if (sl.gen.load(std::memory_order_acquire) != gen) {
+        char const *v = getenv(name);
+        sl.val.store(v ? strdup(v) : nullptr, std::memory_order_release); // (a few bytes per reload are never freed)
+        sl.gen.store(gen, std::memory_order_release);
+      }
+      return sl.val.load(std::memory_order_acquire);
+    }
+  }
+  return getenv(name); // table full: uncached
+}
 } // namespace ffb
 
 using namespace ffb;
 
 extern "C" {
+
+void ffb_reload_env(void) { g_env_gen.fetch_add(1, std::memory_order_acq_rel); }
 
 char const *ffb_last_error(void) { return g_err; }
 
@@ -35,14 +72,22 @@ char const *ffb_version(void) {
 }
 
 int ffb_check_device(void) {
+  // called at the top of the stand-alone row operators: remember which devices passed (cudaGetDeviceProperties is slow)
+  static std::atomic<unsigned long long> ok_mask{0};
   int dev = 0;
   FFB_CUDA_TRY(cudaGetDevice(&dev));
-  cudaDeviceProp p;
-  FFB_CUDA_TRY(cudaGetDeviceProperties(&p, dev));
-  if (p.major != 10) {
-    set_error("device %s is sm_%d%d; this library only contains sm_100a code and has no fallback", p.name,
-              p.major, p.minor);
+  if (dev >= 0 && dev < 64 && ((ok_mask.load(std::memory_order_acquire) >> dev) & 1ULL)) {
+    return FFB_OK;
+  }
+  int major = 0, minor = 0;
+  FFB_CUDA_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+  FFB_CUDA_TRY(cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev));
+  if (major != 10) {
+    set_error("device %d is sm_%d%d; this library only contains sm_100a code and has no fallback", dev, major, minor);
     return FFB_ERR_UNSUPPORTED;
+  }
+  if (dev >= 0 && dev < 64) {
+    ok_mask.fetch_or(1ULL << dev, std::memory_order_release);
   }
   return FFB_OK;
 }
@@ -51,7 +96,7 @@ int ffb_check_device(void) {
 // kernel (attn_multi.cu), kept as the in-tree comparison point.
 static int launch_multi_dispatch(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, void *out, int T,
                                  int kv_len_max, int q_len_max, AtcReq const *reqs, int nreq, cudaStream_t s) {
-  char const *e = getenv("FFB_ATTN_TC");
+  char const *e = ffb::env("FFB_ATTN_TC");
   bool const want_tc = !(e && e[0] == '0');
   if (want_tc && attn_tc_supported(h)) {
     int const rc = launch_attn_tc(h, meta, out, T, reqs, nreq, s);
@@ -299,7 +344,7 @@ int check_common(ffb_attn_t h, ffb_batch_config const *bc, void const *meta, voi
 }
 
 int forced_kernel() { // FFB_FORCE_ATTN=decode|multi (tests / profiling)
-  char const *e = getenv("FFB_FORCE_ATTN");
+  char const *e = ffb::env("FFB_FORCE_ATTN");
   if (!e) {
     return 0;
   }

@@ -90,13 +90,13 @@ int ffb_linear_forward(ffb_linear_t h, void const *in, void *out, void const *w,
   ffb_linear_desc const &d = h->d;
   cudaStream_t s = (cudaStream_t)stream;
   // FFB_LINEAR=stream|tc forces a path (tests / profiling)
-  char const *force = getenv("FFB_LINEAR");
+  char const *force = ffb::env("FFB_LINEAR");
   // Dense weights: up to 16 tokens the persistent bulk-copy GEMV, above that the tcgen05 kernels: at 17..128 tokens one
   // 128-row tile per 128 output features streams the weights once (7B qkv_proj at 64 tokens: 23 us against 65 us in
   // the mma.sync stream kernel) - provided there are enough feature tiles to pull from HBM with (o_proj, 32 tiles:
   // only from 48 tokens).  Quantised weights: in-register dequantisation in the stream kernel up to 64 tokens,
   // dequantise-then-GEMM above.  Env FFB_TC_MIN overrides.
-  static int const tc_min_env = getenv("FFB_TC_MIN") ? atoi(getenv("FFB_TC_MIN")) : 0;
+  static int const tc_min_env = ffb::env("FFB_TC_MIN") ? atoi(ffb::env("FFB_TC_MIN")) : 0;
   int const tc_min = tc_min_env > 0 ? tc_min_env : (d.quant_type != FFB_DT_NONE ? 65 : (d.out_dim >= 8192 ? 17 : 48));
   bool use_tc = h->tc && batch >= tc_min;
   if (force && strcmp(force, "stream") == 0) {
@@ -147,8 +147,8 @@ int ffb_linear_forward_allreduce(ffb_linear_t h, ffb_comm_t comm, void const *in
   }
   ffb_linear_desc const &d = h->d;
   PeerTable const *pt = comm_peer_table(comm);
-  char const *force = getenv("FFB_LINEAR");
-  if (!force && !getenv("FFB_DISABLE_FUSED_ALLREDUCE") &&
+  char const *force = ffb::env("FFB_LINEAR");
+  if (!force && !ffb::env("FFB_DISABLE_FUSED_ALLREDUCE") &&
       linear_gemv_allreduce_supported(pt, d.quant_type, batch, d.in_dim, d.out_dim)) {
     return launch_linear_gemv_allreduce(pt, d.dtype, in, out, w, bias, batch, d.in_dim, d.out_dim, (cudaStream_t)stream);
   }

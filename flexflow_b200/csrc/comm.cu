@@ -112,7 +112,7 @@ void peer_setup(ffb_comm_s *c, NcclApi *api) {
   };
   Rec mine, all[kPeerMaxRanks];
   memset(&mine, 0, sizeof(mine));
-  bool ok = getenv("FFB_DISABLE_PEER") == nullptr;
+  bool ok = ffb::env("FFB_DISABLE_PEER") == nullptr;
   if (ok && cudaMalloc(&c->peer_local, total) != cudaSuccess) {
     c->peer_local = nullptr;
     cudaGetLastError();
@@ -251,7 +251,7 @@ int ffb_allreduce(ffb_comm_t c, void const *in, void *out, size_t count, int dty
   // messages up to 16 MiB on a peer-mapped communicator: two-shot allreduce over NVLink peer memory (peer_allreduce.cu);
   // FFB_DISABLE_PEER_ALLREDUCE=1 keeps the NCCL call (A/B, parity tests).  Every rank must take the same branch: the
   // condition depends only on values that are equal on all ranks (count, dtype, the agreed peer_ok) and this variable.
-  static bool const peer_off = getenv("FFB_DISABLE_PEER_ALLREDUCE") != nullptr;
+  static bool const peer_off = ffb::env("FFB_DISABLE_PEER_ALLREDUCE") != nullptr;
   if (!peer_off && c->peer_ok && ffb::peer_allreduce_supported(&c->peer, count, dtype)) {
     return ffb::launch_peer_allreduce(&c->peer, in, out, count, dtype, (cudaStream_t)stream);
   }

@@ -16,6 +16,10 @@ namespace ffb {
 
 // ---- error plumbing (the reference asserts/exits; the C ABI returns codes) ----
 void set_error(char const *fmt, ...);
+// Cached getenv for the FFB_* override variables (tests, A/B experiments, profiling): the environment is read once per
+// variable and call site, not on every hot call.  `name` must be a string literal (the cache is keyed by its address).
+// A process that changes such a variable after the library has read it calls ffb_reload_env().
+char const *env(char const *name);
 #define FFB_CUDA_TRY(expr)                                                                  \
   do {                                                                                      \
     cudaError_t _e = (expr);                                                                \

@@ -225,7 +225,7 @@ linear_gemv_kernel(T const *__restrict__ A, T const *__restrict__ W, T const *__
 } // namespace
 
 int linear_gemv_supported(int quant, int M, int K, int N) {
-  if (getenv("FFB_DISABLE_GEMV")) {
+  if (ffb::env("FFB_DISABLE_GEMV")) {
     return 0;
   }
   return quant == FFB_DT_NONE && M >= 1 && M <= 16 && (K == 512 || K == 1024 || K == 2048 || K == 4096) && N % GV_BN == 0;

@@ -319,7 +319,7 @@ linear_qgemv_kernel(__half const *__restrict__ A, uint8_t const *__restrict__ W,
 } // namespace
 
 int linear_qgemv_supported(int dtype, int quant, int M, int K, int N) {
-  if (getenv("FFB_DISABLE_QGEMV")) {
+  if (ffb::env("FFB_DISABLE_QGEMV")) {
     return 0;
   }
   return dtype == FFB_DT_HALF && (quant == FFB_DT_INT8 || quant == FFB_DT_INT4) && M >= 1 && M <= 16 &&

@@ -293,7 +293,7 @@ int launch_linear_stream(int dtype, int quant, void const *in, void *out, void c
   FFB_REQUIRE(M >= 1 && M <= 64, "linear_stream handles 1..64 rows, got %d", M);
   int const MT = M <= 16 ? 1 : (M <= 32 ? 2 : 4);
   int NT = (N / 32 >= 2 * kNumSMs) ? 4 : 2;
-  if (char const *e = getenv("FFB_LS_NT")) {
+  if (char const *e = ffb::env("FFB_LS_NT")) {
     NT = atoi(e) == 4 ? 4 : 2;
   }
   dim3 grid(N / (NT * 8));

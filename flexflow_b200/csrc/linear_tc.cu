@@ -190,7 +190,7 @@ struct LinearTcState {
 
 int linear_tc_supported(int dtype, int quant, int K, int N) {
   (void)quant;
-  if (getenv("FFB_DISABLE_TC")) {
+  if (ffb::env("FFB_DISABLE_TC")) {
     return 0;
   }
   return (dtype == FFB_DT_HALF || dtype == FFB_DT_BF16) && K % TC_BK == 0 && N % 16 == 0;
@@ -214,7 +214,7 @@ LinearTcState *linear_tc_create(int dtype, int quant, int K, int N, int max_batc
     }
   }
   // split-K only pays when the output has fewer 256 x 256 tiles than SM pairs at some batch size <= max_batch
-  if (max_batch > 128 && (N + 255) / 256 < kNumSMs / 2 && !getenv("FFB_DISABLE_TC2_SPLITK")) {
+  if (max_batch > 128 && (N + 255) / 256 < kNumSMs / 2 && !ffb::env("FFB_DISABLE_TC2_SPLITK")) {
     if (cudaMalloc(&st->splitk_ws, linear_tc2_ws_bytes()) != cudaSuccess ||
         cudaMalloc((void **)&st->splitk_cnt, linear_tc2_cnt_bytes()) != cudaSuccess ||
         cudaMemset(st->splitk_cnt, 0, linear_tc2_cnt_bytes()) != cudaSuccess) {

@@ -420,7 +420,7 @@ int launch_one(void const *in, void *out, void const *w, void const *bias, int d
   static int calls = 0;
   cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
   cudaStreamIsCapturing(s, &cap);
-  if (getenv("FFB_TC2_TRACE") && cap == cudaStreamCaptureStatusNone && ++calls % 8 == 0) {
+  if (ffb::env("FFB_TC2_TRACE") && cap == cudaStreamCaptureStatusNone && ++calls % 8 == 0) {
     long long host[8][16];
     cudaStreamSynchronize(s);
     cudaMemcpyFromSymbol(host, g_tc2_trace, sizeof(host));
@@ -439,7 +439,7 @@ int launch_one(void const *in, void *out, void const *w, void const *bias, int d
 } // namespace
 
 int linear_tc2_supported(int dtype, int M, int K, int N) {
-  if (getenv("FFB_DISABLE_TC2")) {
+  if (ffb::env("FFB_DISABLE_TC2")) {
     return 0;
   }
   return (dtype == FFB_DT_HALF || dtype == FFB_DT_BF16) && M > 0 && K % T2_BK == 0 && N % 16 == 0;
@@ -463,7 +463,7 @@ int launch_linear_tc2(int dtype, void const *in, void *out, void const *w, void 
   long const mt = (M + 255) / 256;
   int bn = 128, split = 1;
   double best = -1.0;
-  static double const merge_cost = getenv("FFB_TC2_MERGE_COST") ? atof(getenv("FFB_TC2_MERGE_COST")) : 64.0;
+  static double const merge_cost = ffb::env("FFB_TC2_MERGE_COST") ? atof(ffb::env("FFB_TC2_MERGE_COST")) : 64.0;
   for (int S = 1; S <= (ws && cnt ? 2 : 1); S++) {
     if (S > 1 && num_k / S < 8) {
       break;
@@ -484,13 +484,13 @@ int launch_linear_tc2(int dtype, void const *in, void *out, void const *w, void 
       }
     }
   }
-  if (char const *e = getenv("FFB_TC2_BN")) {
+  if (char const *e = ffb::env("FFB_TC2_BN")) {
     int v = atoi(e);
     if (v >= 16 && v <= 256 && v % 16 == 0) {
       bn = v;
     }
   }
-  if (char const *e = getenv("FFB_TC2_SPLIT")) {
+  if (char const *e = ffb::env("FFB_TC2_SPLIT")) {
     int v = atoi(e);
     if (v >= 1 && v <= 2 && (v == 1 || (ws && cnt))) { // S - 1 partials of 512 x BN bytes live in the idle ring
       split = v;

@@ -323,14 +323,14 @@ int linear_tc4_pick_bn(int M, int N) {
 }
 
 int linear_tc4_supported(int dtype, int M, int K, int N) {
-  static bool const on = getenv("FFB_TC4") != nullptr && atoi(getenv("FFB_TC4")) != 0;
+  static bool const on = ffb::env("FFB_TC4") != nullptr && atoi(ffb::env("FFB_TC4")) != 0;
   return on && (dtype == FFB_DT_HALF || dtype == FFB_DT_BF16) && M > 128 && K % T2_BK == 0 && N % 16 == 0 &&
          linear_tc4_pick_bn(M, N) != 0;
 }
 
 int launch_linear_tc4(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N, cudaStream_t s) {
   int bn = linear_tc4_pick_bn(M, N);
-  if (char const *e = getenv("FFB_TC4_BN")) {
+  if (char const *e = ffb::env("FFB_TC4_BN")) {
     int const v = atoi(e);
     if (v >= 16 && v <= 256 && v % 16 == 0 && ((N + v - 1) / v) % 2 == 0) {
       bn = v;

@@ -47,6 +47,7 @@ SIGNATURES = {
     "ffb_last_error": (C.c_char_p, []),
     "ffb_version": (C.c_char_p, []),
     "ffb_check_device": (_i, []),
+    "ffb_reload_env": (None, []),
     "ffb_attn_create": (_i, [C.POINTER(AttnDesc), C.POINTER(_vp)]),
     "ffb_attn_destroy": (_i, [_vp]),
     "ffb_attn_device_bytes": (_sz, [_vp]),
@@ -120,6 +121,11 @@ def load():
         fn.argtypes = args
     _lib = lib
     return lib
+
+
+def reload_env():
+    """Have the library read its FFB_* override variables again (they are cached at first use)."""
+    load().ffb_reload_env()
 
 
 def check(rc, what=""):

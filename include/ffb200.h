@@ -32,6 +32,9 @@ char const *ffb_last_error(void);
 char const *ffb_version(void);
 /* Device sanity check: FFB_OK only on compute capability 10.x. There is no CPU fallback. */
 int ffb_check_device(void);
+/* The FFB_* environment overrides (kernel selection for tests / A-B runs, profiling hooks) are read once and cached; a
+ * process that changes one after the library has seen it calls this to have them read again. */
+void ffb_reload_env(void);
 
 /* ------------------------------------------------------------------------------------------
  * Attention operator state.  Plays the role of IncMultiHeadSelfAttentionMeta /

@@ -8,6 +8,7 @@ import pytest
 
 import ffb_testlib as TL
 from flexflow_b200 import batch_config as B
+from flexflow_b200 import lib as ffb_lib  # noqa: E402
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-2
@@ -29,6 +30,7 @@ def _qkv(*a, **k):
 def test_inc_decode(dt, nq, nkv, dh, force, monkeypatch):
     if force:
         monkeypatch.setenv("FFB_FORCE_ATTN", force)
+        ffb_lib.reload_env()
     rng = np.random.default_rng(10)
     p = _pair(B.INC_DECODING_MODE, dt, nq, nkv, dh, 8, 700, 64)
     lens = {0: 1, 2: 77, 3: 300, 5: 689, 6: 64}
@@ -129,6 +131,7 @@ def test_tree_verify_ragged_stream_k(dt, nq, nkv, dh, tc, monkeypatch):
     (split records + last-arriver merge), several row tiles per request (GQA), a prompt chunk in the same batch.
     tc=0 runs the same batch through the mma.sync kernel."""
     monkeypatch.setenv("FFB_ATTN_TC", tc)
+    ffb_lib.reload_env()
     rng = np.random.default_rng(21)
     p = _pair(B.TREE_VERIFY_MODE, dt, nq, nkv, dh, 8, 3100, 512)
     lens = {0: 3000, 1: 50, 3: 700, 4: 1500, 6: 129, 7: 2047}

@@ -5,6 +5,7 @@ import numpy as np
 import pytest
 
 from flexflow_b200 import batch_config as B
+from flexflow_b200 import lib as ffb_lib  # noqa: E402
 from oracle import oracle as O
 
 pytestmark = pytest.mark.gpu
@@ -86,6 +87,7 @@ def test_linear_stream_dequantises_bit_exactly(quant, monkeypatch):
     torch = _torch()
     from flexflow_b200 import ops
     monkeypatch.setenv("FFB_LINEAR", "stream")
+    ffb_lib.reload_env()
     K, N = 256, 96
     rng = np.random.default_rng(5)
     w = (rng.standard_normal((N, K)) * 0.05).astype(np.float32)
@@ -110,6 +112,7 @@ def test_linear_stream(dtype, quant, M, monkeypatch):
     torch = _torch()
     from flexflow_b200 import ops
     monkeypatch.setenv("FFB_LINEAR", "stream")
+    ffb_lib.reload_env()
     tdt = torch.float16 if dtype == "half" else torch.bfloat16
     K, N = 1024, 1536
     rng = np.random.default_rng(21)
@@ -215,6 +218,7 @@ def test_linear_qgemv_dequantises_bit_exactly(quant, K, N, monkeypatch):
     torch = _torch()
     from flexflow_b200 import ops
     monkeypatch.setenv("FFB_LINEAR", "qgemv")
+    ffb_lib.reload_env()
     rng = np.random.default_rng(K + quant)
     w = (rng.standard_normal((N, K)) * 0.05).astype(np.float32)
     blob = O.quantize(w, quant)
@@ -234,6 +238,7 @@ def test_linear_qgemv_matches_oracle(quant, M, K, N, monkeypatch):
     torch = _torch()
     from flexflow_b200 import ops
     monkeypatch.setenv("FFB_LINEAR", "qgemv")
+    ffb_lib.reload_env()
     rng = np.random.default_rng(M + K)
     x = O.round_to_dt(rng.standard_normal((M, K)).astype(np.float32), "half")
     w = (rng.standard_normal((N, K)) * 0.05).astype(np.float32)
@@ -263,6 +268,7 @@ def test_linear_qgemv_zero_scale_takes_the_elementwise_rule(quant, monkeypatch):
     torch = _torch()
     from flexflow_b200 import ops
     monkeypatch.setenv("FFB_LINEAR", "qgemv")
+    ffb_lib.reload_env()
     K, N = 2048, 96
     rng = np.random.default_rng(3)
     w = (rng.standard_normal((N, K)) * 0.05).astype(np.float32)

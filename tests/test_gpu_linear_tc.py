@@ -4,6 +4,7 @@ import numpy as np
 import pytest
 
 from flexflow_b200 import batch_config as B
+from flexflow_b200 import lib as ffb_lib  # noqa: E402
 from oracle import oracle as O
 
 pytestmark = pytest.mark.gpu
@@ -15,6 +16,7 @@ def test_linear_tc_fp(dtype, M, K, N, monkeypatch):
     import torch
     from flexflow_b200 import ops
     monkeypatch.setenv("FFB_LINEAR", "tc")
+    ffb_lib.reload_env()
     tdt = torch.float16 if dtype == "half" else torch.bfloat16
     rng = np.random.default_rng(31)
     x = O.round_to_dt(rng.standard_normal((M, K)).astype(np.float32), dtype)
@@ -40,8 +42,10 @@ def test_linear_tc2_pair_tiles(M, K, N, bn, monkeypatch):
     import torch
     from flexflow_b200 import ops
     monkeypatch.setenv("FFB_LINEAR", "tc")
+    ffb_lib.reload_env()
     if bn != "auto":
         monkeypatch.setenv("FFB_TC2_BN", bn)  # widths that do not divide N exercise the partial last column tile
+        ffb_lib.reload_env()
     rng = np.random.default_rng(33)
     x = O.round_to_dt(rng.standard_normal((M, K)).astype(np.float32), "half")
     w = O.round_to_dt((rng.standard_normal((N, K)) * 0.05).astype(np.float32), "half")
@@ -67,9 +71,12 @@ def test_linear_tc2_split_k(M, K, N, bias, split, monkeypatch):
     import torch
     from flexflow_b200 import ops
     monkeypatch.setenv("FFB_LINEAR", "tc")
+    ffb_lib.reload_env()
     if split != "auto":
         monkeypatch.setenv("FFB_TC2_SPLIT", split)
+        ffb_lib.reload_env()
         monkeypatch.setenv("FFB_TC2_BN", "256" if N >= 1024 else "128")
+        ffb_lib.reload_env()
     rng = np.random.default_rng(35)
     x = O.round_to_dt(rng.standard_normal((M, K)).astype(np.float32), "half")
     w = O.round_to_dt((rng.standard_normal((N, K)) * 0.05).astype(np.float32), "half")
@@ -97,6 +104,7 @@ def test_linear_tc_quantised_matches_stream(quant, monkeypatch):
     import torch
     from flexflow_b200 import ops
     monkeypatch.setenv("FFB_LINEAR", "tc")
+    ffb_lib.reload_env()
     M, K, N = 300, 1024, 512
     rng = np.random.default_rng(32)
     x = O.round_to_dt(rng.standard_normal((M, K)).astype(np.float32), "half")

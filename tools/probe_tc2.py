@@ -7,6 +7,7 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from flexflow_b200 import ops  # noqa: E402
+from flexflow_b200 import lib as ffb_lib  # noqa: E402
 from tools.bench_linear import time_ms  # noqa: E402
 
 
@@ -26,7 +27,9 @@ def main():
         out = torch.empty(M, N, device="cuda", dtype=torch.float16)
         m = ops.LinearMeta(h, K, N, max_tokens_per_batch=1024)
         os.environ["FFB_TC2_BN"] = str(bn)
+        ffb_lib.reload_env()
         os.environ["FFB_TC2_SPLIT"] = str(S)
+        ffb_lib.reload_env()
         r = []
         for rot in (6, 1):
             i = [0]

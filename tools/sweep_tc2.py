@@ -6,6 +6,7 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from flexflow_b200 import ops  # noqa: E402
+from flexflow_b200 import lib as ffb_lib  # noqa: E402
 from tools.bench_linear import time_ms  # noqa: E402
 
 
@@ -19,8 +20,10 @@ def main():
     for bn in ["auto", 96, 112, 128, 144, 160, 168, 176, 192, 208, 224, 240, 256]:
         if bn == "auto":
             os.environ.pop("FFB_TC2_BN", None)
+            ffb_lib.reload_env()
         else:
             os.environ["FFB_TC2_BN"] = str(bn)
+            ffb_lib.reload_env()
         i = [0]
 
         def fn():

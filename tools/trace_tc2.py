@@ -6,9 +6,11 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from flexflow_b200 import ops  # noqa: E402
+from flexflow_b200 import lib as ffb_lib  # noqa: E402
 
 M, K, N = (int(x) for x in sys.argv[1:4])
 os.environ["FFB_TC2_TRACE"] = "1"
+ffb_lib.reload_env()
 h = ops.FFHandler("cuda:0")
 ws = [(torch.randn(N, K, device="cuda") * 0.02).half() for _ in range(4)]
 x = torch.randn(M, K, device="cuda").half()
