@@ -392,3 +392,31 @@ def test_linear_against_the_reference_cublas_call(M, K, N):
     assert err_ours < 2e-3, err_ours
     assert err_ours <= err_ref + 1e-4, (err_ours, err_ref)
     assert (got.double() - want.double()).abs().max().item() / scale < 1e-2 + 2 * err_ref
+
+
+@pytest.mark.parametrize("quant", [0, 8, 4])
+@pytest.mark.parametrize("M", [16, 64, 512])
+@pytest.mark.parametrize("K,N", [(4096, 11008), (11008, 4096)])
+def test_linear_mlp_projection_shapes(K, N, M, quant):
+    """gate / up (4096 -> 11008) and down (11008 -> 4096) of the LLaMA-2-7B MLP go through the same
+    ffb_linear_forward (the reference runs them through the same Kernels::Linear::forward_kernel): every dispatch range,
+    dense and quantised, against a torch fp32 product of the same (dequantised) 16-bit weights."""
+    torch = _torch()
+    from flexflow_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(K + N + M + quant)
+    x = torch.randn(M, K, generator=g, device="cuda", dtype=torch.float16)
+    w = torch.randn(N, K, generator=g, device="cuda") * 0.02
+    h = ops.FFHandler("cuda:0")
+    if quant == 0:
+        wdev, qt, wref = w.half(), B.DT_NONE, w.half().float()
+    else:
+        blob = O.quantize(w.cpu().numpy(), quant)
+        wdev, qt = torch.from_numpy(blob).cuda(), (B.DT_INT8 if quant == 8 else B.DT_INT4)
+        wref = ops.decompress_weights(wdev, K, N, qt).float()
+    m = ops.LinearMeta(h, K, N, torch.float16, qt, 512)
+    out = torch.full((M, N), float("nan"), dtype=torch.float16, device="cuda")
+    ops.Linear.inference_kernel_wrapper(m, None, x, out, wdev, None, K, N, M)
+    torch.cuda.synchronize()
+    want = x.float() @ wref.t()
+    assert torch.isfinite(out.float()).all()
+    assert float((out.float() - want).abs().max() / want.abs().max()) < 4e-3
