@@ -24,6 +24,7 @@ SOURCES = [
     "linear_tc.cu",
     "linear_tc2.cu",
     "linear_tc4.cu",
+    "linear_tcq.cu",
     "capi_linear.cu",
     "comm.cu",
     "peer_allreduce.cu",

@@ -7,9 +7,10 @@
 // releases ring slots and finally signals the four epilogue warps, which read the accumulator with
 // tcgen05.ld (32 lanes x 32 columns per instruction), add the bias, convert and store.
 // The reference accumulates in DT (cuBLAS compute type = output type); fp32 here.
-// int8/int4 weights at large M are dequantised once per call into a private DT scratch and fed to the
-// same kernel (what the reference does, minus its host-to-device copy); the M <= 64 path
-// (linear_stream.cu) never materialises them.
+// int8/int4 weights at large M go to linear_tcq.cu (dequantised in shared memory ahead of the MMA); only the cases
+// it does not take (bf16 group meta, N not a multiple of 128) are dequantised once per call into a private DT scratch
+// and fed to this kernel (what the reference does, minus its host-to-device copy); the M <= 64 path
+// (linear_stream.cu) dequantises in registers.
 #include <cuda.h>
 
 #include <new>
@@ -172,6 +173,9 @@ int make_tensor_map_2d(CUtensorMap *tm, int dtype, void const *ptr, long rows, i
 
 
 int linear_tc2_supported(int dtype, int M, int K, int N);
+// linear_tcq.cu: quantised weights dequantised in shared memory ahead of the MMA (half activations)
+int linear_tcq_supported(int dtype, int quant, int K, int N);
+int launch_linear_tcq(int quant, void const *in, void *out, void const *blob, void const *bias, int M, int K, int N, cudaStream_t s);
 // linear_tc4.cu: the same SM-pair tiles in clusters of two pairs sharing A by TMA multicast (FFB_TC4=1)
 int linear_tc4_supported(int dtype, int M, int K, int N);
 int launch_linear_tc4(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N, cudaStream_t s);
@@ -205,7 +209,9 @@ LinearTcState *linear_tc_create(int dtype, int quant, int K, int N, int max_batc
     return nullptr;
   }
   st->dtype = dtype; st->quant = quant; st->K = K; st->N = N; st->max_batch = max_batch;
-  if (quant != FFB_DT_NONE && max_batch > 64) {
+  // quantised layers: linear_tcq.cu dequantises in shared memory; only shapes / types it does not take (bf16, ragged
+  // N) fall back to dequantise-into-a-scratch + dense GEMM
+  if (quant != FFB_DT_NONE && max_batch > 64 && !linear_tcq_supported(dtype, quant, K, N)) {
     cudaError_t e = cudaMalloc(&st->scratch, (size_t)K * N * 2);
     if (e != cudaSuccess) {
       set_error("cudaMalloc of the dequant scratch failed: %s", cudaGetErrorString(e));
@@ -244,6 +250,9 @@ void linear_tc_destroy(LinearTcState *st) {
 int launch_linear_tc(LinearTcState *st, int dtype, int quant, void const *in, void *out, void const *w,
                      void const *bias, int M, int K, int N, cudaStream_t s) {
   void const *wd = w;
+  if (quant != FFB_DT_NONE && linear_tcq_supported(dtype, quant, K, N)) {
+    return launch_linear_tcq(quant, in, out, w, bias, M, K, N, s);
+  }
   if (quant != FFB_DT_NONE) {
     FFB_REQUIRE(st->scratch, "quantised layer created with max_batch <= 64 has no dequant scratch");
     int rc = quant == FFB_DT_INT4 ? ffb_dequant_int4(w, st->scratch, K, N, dtype, s) : ffb_dequant_int8(w, st->scratch, K, N, dtype, s);

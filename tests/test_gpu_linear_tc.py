@@ -119,3 +119,47 @@ def test_linear_tc_quantised_matches_stream(quant, monkeypatch):
     torch.cuda.synchronize()
     want = O.linear(x, wq, None, "half")
     assert np.abs(out.float().cpu().numpy() - want).max() <= 2e-3 * max(1.0, np.abs(want).max())
+
+
+@pytest.mark.parametrize("quant", [8, 4])
+@pytest.mark.parametrize("M", [65, 300])
+def test_linear_tcq_dequantises_bit_exactly_in_shared_memory(quant, M, monkeypatch):
+    """linear_tcq.cu (M > 64, quantised weights dequantised in shared memory ahead of the tcgen05 MMA): with one-hot
+    activations row m of the output IS column k0 + m of the dequantised matrix (a single fp32 term), so the converter
+    warps' output is compared bit for bit with the oracle's dequantisation - values of every code, scales of both
+    signs and a few degenerate ones (0, inf: the element-wise fallback), every k-block, ragged last M tile; plus a
+    bias."""
+    import torch
+    from flexflow_b200 import ops
+    K, N = 512, 256
+    rng = np.random.default_rng(quant * 100 + M)
+    w = (rng.standard_normal((N, K)) * 0.05).astype(np.float32)
+    blob = O.quantize(w, quant).copy()
+    nv = N * K // (2 if quant == 4 else 1)
+    meta = blob[nv:].view(np.uint16)
+    ng = N * K // 32
+    sc = meta[ng:]
+    sc[5], sc[77], sc[300] = 0x0000, 0x7C00, (sc[300] | 0x8000)  # zero, inf, a negative scale
+    want = O.dequant(blob, quant, K, N).view(np.float16)  # [N][K]
+    h = ops.FFHandler("cuda:0")
+    m = ops.LinearMeta(h, K, N, quantization_type=B.DT_INT8 if quant == 8 else B.DT_INT4, max_tokens_per_batch=512)
+    bdev = torch.from_numpy(blob).cuda()
+    bias = torch.from_numpy(rng.standard_normal(N).astype(np.float16)).cuda()
+    for k0 in range(0, K, M):
+        n = min(M, K - k0)
+        x = torch.zeros(M, K, dtype=torch.float16, device="cuda")
+        x[torch.arange(n), k0 + torch.arange(n)] = 1.0
+        out = torch.full((M, N), float("nan"), dtype=torch.float16, device="cuda")
+        ops.Linear.inference_kernel_wrapper(m, None, x, out, bdev, None, K, N, M)
+        got = out[:n].cpu().numpy()
+        exp = want[:, k0:k0 + n].T
+        fin = np.isfinite(exp.astype(np.float32))
+        assert (got.view(np.uint16)[fin] == exp.view(np.uint16)[fin]).all(), k0
+        assert not np.isfinite(got.astype(np.float32)[~fin]).any()
+        if n < M:
+            assert (out[n:].float() == 0).all()
+    out_b = torch.empty(M, N, dtype=torch.float16, device="cuda")
+    ops.Linear.inference_kernel_wrapper(m, None, x, out_b, bdev, bias, K, N, M)
+    torch.cuda.synchronize()
+    ok = torch.isfinite(out.float()) & torch.isfinite(out_b.float())
+    assert torch.equal(out_b[ok], (out.float() + bias.float()[None, :]).half()[ok])
