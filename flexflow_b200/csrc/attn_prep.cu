@@ -19,6 +19,9 @@ prep_kernel(T const *__restrict__ qkv, T *__restrict__ q_buf, T *__restrict__ k_
             ffb_combined_batch_config_meta const *__restrict__ meta, int mode, int nq, int nkv,
             int cache_len, int max_requests, RopeParams rp, int scaling_query, float scaling_factor,
             int num_generation_tokens) {
+  // the attention kernel that follows is launched as a programmatic dependent: let it start its set-up (and the
+  // stream of K/V rows older than this batch) now; it waits for this grid before it touches anything written here
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   int const t = blockIdx.x;
   int const H = nq * DH;
   int const G = nq / nkv;

@@ -57,6 +57,7 @@ struct AtcEntry {
   short slot, mt; // request slot, row-tile index inside the request
   short ntiles;   // key tiles of 128 covering the longest row of the tile
   short qlen;     // query tokens of the request in this batch
+  int first_new;  // first cache row of the request that THIS batch's prep kernel writes (rows below it are older)
 };
 struct AtcSched {
   int n_ent;     // entries in use
@@ -191,9 +192,18 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
       SegWalk w;
       w.init(sched);
       int j = 0; // ring item counter: K tile, V tile, K tile, ...
+      // Programmatic dependent launch: this grid may start while the prep kernel (RoPE + KV append of THIS batch) is
+      // still running.  Cache rows below first_new are older than that kernel, so their tiles stream at once; the
+      // first tile that reaches into the new rows waits for the prep grid (griddepcontrol.wait, once).
+      bool prep_done = false;
       while (w.next(sched)) {
         int const row_base = ((int)sched.ent[w.e].slot * nkv + w.kvh) * cache_len;
+        int const first_new = sched.ent[w.e].first_new;
         for (int t = w.t0; t < w.t1; t++) {
+          if (!prep_done && (t + 1) * TBN > first_new) {
+            asm volatile("griddepcontrol.wait;" ::: "memory");
+            prep_done = true;
+          }
 #pragma unroll
           for (int kv = 0; kv < 2; kv++, j++) {
             int const sb = j % NBUF;
@@ -347,6 +357,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
         mbar_arrive(&q_full);
       };
 
+      // q_buf / qdesc come from the prep kernel of this batch (see the producer)
+      asm volatile("griddepcontrol.wait;" ::: "memory");
       SegWalk w;
       w.init(sched);
       bool have = w.next(sched);
@@ -781,6 +793,8 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
       e.mt = (short)mt;
       e.ntiles = (short)ntiles;
       e.qlen = (short)rq.qlen;
+      // beam mode places new rows by the bit-mask sizes (spec_…cu:343-346), not at first_depth: no early streaming there
+      e.first_new = d.mode == FFB_BEAM_SEARCH_MODE ? 0 : std::max(0, rq.first_depth);
       cum += d.num_kv_heads * ntiles;
     }
   }
@@ -868,13 +882,28 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
   if (h->profiling) {
     cudaEventRecord(h->ev0, s);
   }
+  // launched as a programmatic dependent of the preceding kernel in the stream (the prep kernel, which signals
+  // griddepcontrol.launch_dependents at once): set-up and the stream of old K/V tiles overlap its execution.
+  // FFB_ATC_PDL=0 launches it the ordinary way.
+  static bool const pdl = !(env("FFB_ATC_PDL") && env("FFB_ATC_PDL")[0] == '0');
 #define FFB_ATC(TT, DH)                                                                                              \
   do {                                                                                                               \
     size_t const smem = AtcCfg<DH>::SMEM;                                                                            \
     FFB_SET_MAX_SMEM_ONCE((attn_tc_kernel<TT, DH>), smem);                                                           \
-    attn_tc_kernel<TT, DH><<<grid, ATC_THREADS, smem, s>>>(tmK, tmV, sc, (TT const *)h->q_buf, h->qdesc, meta,       \
-                                                            h->partial, h->split_counter, (TT *)out, d.num_q_heads,   \
-                                                            d.num_kv_heads, h->cache_len, scale_log2, tracing ? trace : nullptr); \
+    cudaLaunchConfig_t cfg = {};                                                                                     \
+    cfg.gridDim = dim3(grid);                                                                                        \
+    cfg.blockDim = dim3(ATC_THREADS);                                                                                \
+    cfg.dynamicSmemBytes = smem;                                                                                     \
+    cfg.stream = s;                                                                                                  \
+    cudaLaunchAttribute attr[1];                                                                                     \
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                                                 \
+    attr[0].val.programmaticStreamSerializationAllowed = 1;                                                          \
+    cfg.attrs = attr;                                                                                                \
+    cfg.numAttrs = pdl ? 1 : 0;                                                                                      \
+    FFB_CUDA_TRY(cudaLaunchKernelEx(&cfg, attn_tc_kernel<TT, DH>, tmK, tmV, sc, (TT const *)h->q_buf,                \
+                                    (QueryDesc const *)h->qdesc, meta, h->partial, h->split_counter, (TT *)out,      \
+                                    d.num_q_heads, d.num_kv_heads, h->cache_len, scale_log2,                         \
+                                    tracing ? trace : (long long *)nullptr));                                        \
   } while (0)
   if (d.dtype == FFB_DT_HALF) {
     if (d.head_dim == 128) FFB_ATC(__half, 128); else FFB_ATC(__half, 64);

@@ -466,7 +466,9 @@ softmax_kernel(T const *__restrict__ in, T *__restrict__ out, int V) {
       }
     }
     mx = block_reduce(mx, true);
-    float const base = mx == -INFINITY ? 0.f : mx * kLog2e;
+    // (x - max) first, then the scale: exact for x = max whatever the magnitude (an fma against a rounded max * log2e
+    // leaves a residue of |max| * 2^-24 in the exponent, harmless for logits, fatal for rows like -1e30)
+    float const base = mx == -INFINITY ? 0.f : mx;
     float sum = 0.f;
 #pragma unroll
     for (int u = 0; u < SM_VEC; u++) {
@@ -474,7 +476,7 @@ softmax_kernel(T const *__restrict__ in, T *__restrict__ out, int V) {
       if (c < nvec) {
 #pragma unroll
         for (int e = 0; e < 8; e++) {
-          f[u][e] = ffb_ex2(fmaf(f[u][e], kLog2e, -base));
+          f[u][e] = ffb_ex2((f[u][e] - base) * kLog2e);
           sum += f[u][e];
         }
       }
@@ -500,15 +502,15 @@ softmax_kernel(T const *__restrict__ in, T *__restrict__ out, int V) {
     mx = fmaxf(mx, DT<T>::to_f(p[i]));
   }
   mx = block_reduce(mx, true);
-  float const base = mx == -INFINITY ? 0.f : mx * kLog2e;
+  float const base = mx == -INFINITY ? 0.f : mx;
   float sum = 0.f;
   for (int i = tid; i < V; i += SM_THREADS) {
-    sum += ffb_ex2(fmaf(DT<T>::to_f(p[i]), kLog2e, -base));
+    sum += ffb_ex2((DT<T>::to_f(p[i]) - base) * kLog2e);
   }
   sum = block_reduce(sum, false);
   float const inv = 1.f / sum;
   for (int i = tid; i < V; i += SM_THREADS) {
-    q[i] = DT<T>::from_f(ffb_ex2(fmaf(DT<T>::to_f(p[i]), kLog2e, -base)) * inv);
+    q[i] = DT<T>::from_f(ffb_ex2((DT<T>::to_f(p[i]) - base) * kLog2e) * inv);
   }
 }
 
