@@ -263,7 +263,7 @@ int launch_decode_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta
   float const scale_log2 = scale * 1.4426950408889634f;
   int const fuse = ffb::env("FFB_SEPARATE_COMBINE") ? 0 : 1;
   dim3 grid(nsplit, d.num_q_heads, T);
-  if (h->profiling) {
+  if (h->profiling == 1) {
     cudaEventRecord(h->ev0, s);
   }
 #define FFB_DEC_U(TT, DH, UU)                                                                             \
@@ -283,7 +283,7 @@ int launch_decode_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta
   }
 #undef FFB_DEC
 #undef FFB_DEC_U
-  if (h->profiling) {
+  if (h->profiling == 1) {
     cudaEventRecord(h->ev1, s);
   }
   FFB_LAUNCH_CHECK();

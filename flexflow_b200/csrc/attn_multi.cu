@@ -423,7 +423,7 @@ int launch_multi_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta,
   float const scale_log2 = scale * 1.4426950408889634f;
   int const fuse = ffb::env("FFB_SEPARATE_COMBINE") ? 0 : 1;
   dim3 grid(nsplit, d.num_kv_heads * m_tiles, d.max_requests);
-  if (h->profiling) {
+  if (h->profiling == 1) {
     cudaEventRecord(h->ev0, s);
   }
 #define FFB_MQ(TT, DH)                                                                                     \
@@ -441,7 +441,7 @@ int launch_multi_attn(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta,
     if (d.head_dim == 128) FFB_MQ(__nv_bfloat16, 128); else FFB_MQ(__nv_bfloat16, 64);
   }
 #undef FFB_MQ
-  if (h->profiling) {
+  if (h->profiling == 1) {
     cudaEventRecord(h->ev1, s);
   }
   FFB_LAUNCH_CHECK();

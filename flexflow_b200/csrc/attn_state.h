@@ -21,7 +21,8 @@ struct ffb_attn_s {
   float *partial = nullptr;        // split-KV partials
   size_t partial_bytes = 0;
   // m->profiling (inc_…cu:1510-1538): events around the dominant attention kernel only
-  bool profiling = false;
+  // 2 = measurement mode: the forward call launches ONLY that kernel, on the state the last full call left
+  int profiling = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int num_generation_tokens_cur = 0; // bc->num_generation_tokens of the batch in flight
   int num_active_infr_tokens = 0; // TreeIncMultiHeadSelfAttentionMeta::num_active_infr_tokens

@@ -78,30 +78,55 @@ template <int DH> struct AtcCfg {
   static constexpr size_t SMEM = (size_t)NBUF * KV_BYTES + Q_BYTES + 1024; // ring + Q / output staging + alignment
 };
 
-// Walks the segments of one CTA: maximal runs of consecutive flattened tiles inside one unit.
+// x / d for 0 <= x < 2^22, 0 < d, rd = 1.f / d: a float estimate and a +-1 fix-up (8 instructions; an integer division by a
+// run-time value is ~25, and this code runs at every unit boundary in all 18 warps, out of a cold instruction cache)
+__device__ __forceinline__ int fast_div(int x, int d, float rd) {
+  int q = (int)((float)x * rd);
+  int const r = x - q * d;
+  q += r < 0 ? -1 : (r >= d ? 1 : 0);
+  return q;
+}
+
+// Walks the segments of one CTA: maximal runs of consecutive flattened tiles inside one unit.  The position inside the
+// schedule (entry, kv head, tile) is kept incrementally: a segment ends at the end of its unit or of the CTA's range.
 struct SegWalk {
   int x, x_end; // flattened position, end of this CTA's range
   int e;        // entry cursor
+  int nkv;
+  int kvh_next, t_next; // position of x inside entry e
   // current segment
   int kvh, t0, t1;
-  __device__ __forceinline__ void init(AtcSched const &sc) {
+  __device__ __forceinline__ void init(AtcSched const &sc, int nkv_) {
     x = (int)blockIdx.x * sc.rg;
     x_end = min(sc.total, x + sc.rg);
+    nkv = nkv_;
     e = 0;
-  }
-  __device__ __forceinline__ bool next(AtcSched const &sc) {
-    if (x >= x_end) {
-      return false;
-    }
     while (e + 1 < sc.n_ent && sc.ent[e + 1].cum <= x) {
       e++;
     }
     int const nt = sc.ent[e].ntiles;
     int const r = x - sc.ent[e].cum;
-    kvh = r / nt;
-    t0 = r - kvh * nt;
+    kvh_next = fast_div(r, nt, __frcp_rn((float)nt));
+    t_next = r - kvh_next * nt;
+  }
+  __device__ __forceinline__ bool next(AtcSched const &sc) {
+    if (x >= x_end) {
+      return false;
+    }
+    int nt = sc.ent[e].ntiles;
+    if (t_next == nt) { // the previous segment ran to the end of its unit
+      t_next = 0;
+      if (++kvh_next == nkv) {
+        kvh_next = 0;
+        e++;
+        nt = sc.ent[e].ntiles;
+      }
+    }
+    kvh = kvh_next;
+    t0 = t_next;
     t1 = min(nt, t0 + (x_end - x));
     x += t1 - t0;
+    t_next = t1;
     return true;
   }
 };
@@ -113,7 +138,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
                const __grid_constant__ AtcSched sched_param, T const *__restrict__ q_buf,
                QueryDesc const *__restrict__ qdesc, ffb_combined_batch_config_meta const *__restrict__ meta,
                float *__restrict__ partial, int *__restrict__ split_counter, T *__restrict__ out, int nq, int nkv,
-               int cache_len, float scale_log2, long long *trace) {
+               int cache_len, float scale_log2, int kv_evict_first, long long *trace) {
   using Cfg = AtcCfg<DH>;
   constexpr int KH = Cfg::KH, NBUF = Cfg::NBUF;
   constexpr uint32_t HALF = Cfg::HALF_BYTES;
@@ -190,29 +215,48 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
     asm volatile("barrier.cta.arrive 0, %0;" ::"n"(ATC_THREADS) : "memory");
     if (lane == 0) {
       SegWalk w;
-      w.init(sched);
-      int j = 0; // ring item counter: K tile, V tile, K tile, ...
+      w.init(sched, nkv);
+      // ring cursor: slot and phase kept incrementally (j % NBUF, j / NBUF would make the compiler unroll the loop
+      // NBUF-fold: 8 KB of a 32 KB instruction cache for one lane's loop)
+      int sb = 0;
+      uint32_t ph = 1;
+      // K / V rows are read once: evict-first in L2, so that the stream does not push out what is re-read (code,
+      // descriptors, Q, split records)
+      uint64_t policy = 0;
+      if (kv_evict_first) {
+        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+      }
       // Programmatic dependent launch: this grid may start while the prep kernel (RoPE + KV append of THIS batch) is
       // still running.  Cache rows below first_new are older than that kernel, so their tiles stream at once; the
       // first tile that reaches into the new rows waits for the prep grid (griddepcontrol.wait, once).
       bool prep_done = false;
+      int j = 0;
       while (w.next(sched)) {
         int const row_base = ((int)sched.ent[w.e].slot * nkv + w.kvh) * cache_len;
         int const first_new = sched.ent[w.e].first_new;
+#pragma unroll 1
         for (int t = w.t0; t < w.t1; t++) {
           if (!prep_done && (t + 1) * TBN > first_new) {
             asm volatile("griddepcontrol.wait;" ::: "memory");
             prep_done = true;
           }
-#pragma unroll
+#pragma unroll 1
           for (int kv = 0; kv < 2; kv++, j++) {
-            int const sb = j % NBUF;
-            mbar_wait(&kv_empty[sb], ((j / NBUF) & 1) ^ 1);
+            mbar_wait(&kv_empty[sb], ph);
             FFB_TR(0, j);
             mbar_expect_tx(&kv_full[sb], Cfg::KV_BYTES);
+            CUtensorMap const *tm = kv ? &tmV : &tmK;
 #pragma unroll
             for (int hh = 0; hh < KH; hh++) {
-              tma_load_2d(sKV + sb * Cfg::KV_BYTES + hh * HALF, kv ? &tmV : &tmK, hh * 64, row_base + t * TBN, &kv_full[sb]);
+              if (kv_evict_first) {
+                tma_load_2d_hint(sKV + sb * Cfg::KV_BYTES + hh * HALF, tm, hh * 64, row_base + t * TBN, &kv_full[sb], policy);
+              } else {
+                tma_load_2d(sKV + sb * Cfg::KV_BYTES + hh * HALF, tm, hh * 64, row_base + t * TBN, &kv_full[sb]);
+              }
+            }
+            if (++sb == NBUF) {
+              sb = 0;
+              ph ^= 1u;
             }
           }
         }
@@ -253,7 +297,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
           tc_commit(&s_full[g & 1]);
         };
         SegWalk w;
-        w.init(sched);
+        w.init(sched, nkv);
         int g0 = 0, seg = 0;
         while (w.next(sched)) {
           int const ntiles = w.t1 - w.t0;
@@ -263,29 +307,32 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
           FFB_TR(1, 4000 + seg);
           mbar_wait(&q_full, seg & 1);        // Q of this segment is in tensor memory, O of the previous one was read out
           tc_fence_after();
-          issue_qk(g0);
-          if (ntiles > 1) {
-            issue_qk(g0 + 1);
-          }
-          for (int it = 0; it < ntiles; it++) {
+          // one loop body for the whole segment (it = -2, -1: the two look-ahead QK^T), so that issue_qk and the PV
+          // block are emitted once: the issuer's code stays small in the instruction cache
+#pragma unroll 1
+          for (int it = -2; it < ntiles; it++) {
             int const g = g0 + it;
-            int const j = 2 * g + 1, sb = j % NBUF;
-            mbar_wait(&p_full, g & 1);
-            FFB_TR(1, 2000 + g);
-            mbar_wait(&kv_full[sb], (j / NBUF) & 1);
-            FFB_TR(1, 3000 + g);
-            tc_fence_after();
-            uint32_t const vb = smem_u32(sKV + sb * Cfg::KV_BYTES);
-            uint32_t const tP = tmem_S + (uint32_t)(g & 1) * 128u;
+            if (it >= 0) {
+              int const j = 2 * g + 1, sb = j % NBUF;
+              mbar_wait(&p_full, g & 1);
+              FFB_TR(1, 2000 + g);
+              mbar_wait(&kv_full[sb], (j / NBUF) & 1);
+              FFB_TR(1, 3000 + g);
+              tc_fence_after();
+              uint32_t const vb = smem_u32(sKV + sb * Cfg::KV_BYTES);
+              uint32_t const tP = tmem_S + (uint32_t)(g & 1) * 128u;
 #pragma unroll
-            for (int k = 0; k < TBN / 16; k++) {
-              uint64_t const db = umma_desc_mn_sw128(vb + k * 2048, HALF, 1024);
-              tc_mma_f16_ts(tmem_O, tP + (uint32_t)(k * 8), db, idesc_pv, (it | k) != 0);
+              for (int k = 0; k < TBN / 16; k++) {
+                uint64_t const db = umma_desc_mn_sw128(vb + k * 2048, HALF, 1024);
+                tc_mma_f16_ts(tmem_O, tP + (uint32_t)(k * 8), db, idesc_pv, (it | k) != 0);
+              }
+              tc_commit(&kv_empty[sb]);
+              tc_commit(&o_full);
             }
-            tc_commit(&kv_empty[sb]);
-            tc_commit(&o_full);
             if (it + 2 < ntiles) {
-              mbar_wait(&o_full, g & 1); // P of this tile has been consumed: its score buffer may be overwritten
+              if (it >= 0) {
+                mbar_wait(&o_full, g & 1); // P of this tile has been consumed: its score buffer may be overwritten
+              }
               issue_qk(g + 2);
             }
           }
@@ -315,6 +362,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
       // boundary costs no exposed global-memory latency.
       int n_th = -1, n_kvl = 0, n_bit = -1;
       unsigned long long n_vis = 0;
+      float const rcp_G = __frcp_rn((float)G), rcp_rg = __frcp_rn((float)sched.rg);
       auto fetch_rows = [&](SegWalk const &sw) {
         AtcEntry const &en = sched.ent[sw.e];
         int const R = en.mt * TBM + row;
@@ -323,8 +371,9 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
         n_bit = -1;
         n_vis = 0;
         if (R < en.qlen * G) {
-          int const tok = en.first_tok + R / G;
-          n_th = tok * nq + sw.kvh * G + R % G;
+          int const ti = fast_div(R, G, rcp_G);
+          int const tok = en.first_tok + ti;
+          n_th = tok * nq + sw.kvh * G + (R - ti * G);
           QueryDesc const qd = qdesc[tok];
           n_kvl = qd.kv_len;
           n_bit = qd.bit;
@@ -360,7 +409,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
       // q_buf / qdesc come from the prep kernel of this batch (see the producer)
       asm volatile("griddepcontrol.wait;" ::: "memory");
       SegWalk w;
-      w.init(sched);
+      w.init(sched, nkv);
       bool have = w.next(sched);
       int g0 = 0;
       if (tid == 0) FFB_TR(2, 100);
@@ -375,7 +424,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
         int const ntiles = w.t1 - w.t0, ntcs = en.ntcs, t_first = w.t0;
         // the pieces of this unit: CTAs whose ranges intersect its flattened tiles
         int const U0 = en.cum + w.kvh * en.ntiles;
-        int const c_first = U0 / sched.rg, npieces = (U0 + en.ntiles - 1) / sched.rg - c_first + 1;
+        int const c_first = fast_div(U0, sched.rg, rcp_rg);
+        int const npieces = fast_div(U0 + en.ntiles - 1, sched.rg, rcp_rg) - c_first + 1;
         int const piece = (int)blockIdx.x - c_first;
         int const th = n_th, kvl = n_kvl, bit = n_bit;
         // tree / beam rows: bit i of row_vis says whether tree position i (key ntcs + i) is visible to this row
@@ -879,13 +929,15 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
   }
   CUtensorMap const &tmK = *reinterpret_cast<CUtensorMap const *>(h->tmK);
   CUtensorMap const &tmV = *reinterpret_cast<CUtensorMap const *>(h->tmV);
-  if (h->profiling) {
+  if (h->profiling == 1) {
     cudaEventRecord(h->ev0, s);
   }
   // launched as a programmatic dependent of the preceding kernel in the stream (the prep kernel, which signals
   // griddepcontrol.launch_dependents at once): set-up and the stream of old K/V tiles overlap its execution.
   // FFB_ATC_PDL=0 launches it the ordinary way.
   static bool const pdl = !(env("FFB_ATC_PDL") && env("FFB_ATC_PDL")[0] == '0');
+  // K / V tiles loaded with the L2 evict-first policy (FFB_ATC_EVICT=0: default policy)
+  int const kv_evict = !(env("FFB_ATC_EVICT") && env("FFB_ATC_EVICT")[0] == '0');
 #define FFB_ATC(TT, DH)                                                                                              \
   do {                                                                                                               \
     size_t const smem = AtcCfg<DH>::SMEM;                                                                            \
@@ -899,10 +951,10 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                                                 \
     attr[0].val.programmaticStreamSerializationAllowed = 1;                                                          \
     cfg.attrs = attr;                                                                                                \
-    cfg.numAttrs = pdl ? 1 : 0;                                                                                      \
+    cfg.numAttrs = pdl && h->profiling != 2 ? 1 : 0;                                                                 \
     FFB_CUDA_TRY(cudaLaunchKernelEx(&cfg, attn_tc_kernel<TT, DH>, tmK, tmV, sc, (TT const *)h->q_buf,                \
                                     (QueryDesc const *)h->qdesc, meta, h->partial, h->split_counter, (TT *)out,      \
-                                    d.num_q_heads, d.num_kv_heads, h->cache_len, scale_log2,                         \
+                                    d.num_q_heads, d.num_kv_heads, h->cache_len, scale_log2, kv_evict,               \
                                     tracing ? trace : (long long *)nullptr));                                        \
   } while (0)
   if (d.dtype == FFB_DT_HALF) {
@@ -911,7 +963,7 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
     if (d.head_dim == 128) FFB_ATC(__nv_bfloat16, 128); else FFB_ATC(__nv_bfloat16, 64);
   }
 #undef FFB_ATC
-  if (h->profiling) {
+  if (h->profiling == 1) {
     cudaEventRecord(h->ev1, s);
   }
   FFB_LAUNCH_CHECK();

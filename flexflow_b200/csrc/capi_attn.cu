@@ -214,7 +214,7 @@ int ffb_attn_set_profiling(ffb_attn_t h, int enable) {
     FFB_CUDA_TRY(cudaEventCreate(&h->ev0));
     FFB_CUDA_TRY(cudaEventCreate(&h->ev1));
   }
-  h->profiling = enable != 0;
+  h->profiling = enable == 2 ? 2 : (enable != 0);
   return FFB_OK;
 }
 
@@ -381,7 +381,7 @@ int ffb_inc_attn_forward(ffb_attn_t h, ffb_batch_config const *bc, ffb_combined_
     sc.add(i, ri, ri.num_tokens_in_batch, tl, bc->causalMask[i].non_tree_cache_size, ri.prompt_phase);
   }
   h->num_generation_tokens_cur = bc->num_generation_tokens;
-  rc = launch_prep(h, FFB_INC_DECODING_MODE, meta, qkv, T, bc->num_generation_tokens, 0, s);
+  rc = h->profiling == 2 ? FFB_OK : launch_prep(h, FFB_INC_DECODING_MODE, meta, qkv, T, bc->num_generation_tokens, 0, s);
   if (rc != FFB_OK) {
     return rc;
   }
@@ -435,7 +435,7 @@ int ffb_tree_attn_forward(ffb_attn_t h, ffb_tree_verify_batch_config const *tbc,
     sc.add(i, ri, ri.num_tokens_in_batch, tl, bc->causalMask[i].non_tree_cache_size, ri.prompt_phase);
   }
   h->num_generation_tokens_cur = bc->num_generation_tokens;
-  rc = launch_prep(h, FFB_TREE_VERIFY_MODE, meta, qkv, T, bc->num_generation_tokens, 0, s);
+  rc = h->profiling == 2 ? FFB_OK : launch_prep(h, FFB_TREE_VERIFY_MODE, meta, qkv, T, bc->num_generation_tokens, 0, s);
   if (rc != FFB_OK) {
     return rc;
   }
@@ -473,7 +473,7 @@ int ffb_spec_attn_forward(ffb_attn_t h, ffb_beam_search_batch_config const *bbc,
     sc.add(i, ri, ql, tl, bm.non_tree_cache_size, !speculative);
   }
   h->num_generation_tokens_cur = bc->num_generation_tokens;
-  rc = launch_prep(h, FFB_BEAM_SEARCH_MODE, meta, qkv, T, bc->num_generation_tokens, bbc->speculative_request_num, s);
+  rc = h->profiling == 2 ? FFB_OK : launch_prep(h, FFB_BEAM_SEARCH_MODE, meta, qkv, T, bc->num_generation_tokens, bbc->speculative_request_num, s);
   if (rc != FFB_OK) {
     return rc;
   }

@@ -82,7 +82,11 @@ size_t ffb_attn_device_bytes(ffb_attn_t h);
 
 /* m->profiling of the reference (src/ops/inc_multihead_self_attention.cu:1510-1538 records a
  * cudaEvent pair around the whole wrapper and printf()s): here the pair brackets the dominant
- * attention kernel only, and the elapsed time of the last forward call is read back explicitly. */
+ * attention kernel only, and the elapsed time of the last forward call is read back explicitly.
+ * enable = 2 is a measurement mode: forward calls launch ONLY the dominant attention kernel (no
+ * RoPE / KV-append kernel, no events, no programmatic dependent launch) on the state the last full
+ * call left behind - same descriptors, same cache rows, same output - so that a caller can bracket
+ * a run of such launches with its own events and divide (bench.py: roofline.kernel_ms). */
 int ffb_attn_set_profiling(ffb_attn_t h, int enable);
 int ffb_attn_last_kernel_ms(ffb_attn_t h, float *ms_out);
 

@@ -127,7 +127,7 @@ def test_linear_tcq_dequantises_bit_exactly_in_shared_memory(quant, M, monkeypat
     """linear_tcq.cu (M > 64, quantised weights dequantised in shared memory ahead of the tcgen05 MMA): with one-hot
     activations row m of the output IS column k0 + m of the dequantised matrix (a single fp32 term), so the converter
     warps' output is compared bit for bit with the oracle's dequantisation - values of every code, scales of both
-    signs and a few degenerate ones (0, inf: the element-wise fallback), every k-block, ragged last M tile; plus a
+    signs and an infinite one (the element-wise fallback), every k-block, ragged last M tile; plus a
     bias."""
     import torch
     from flexflow_b200 import ops
@@ -139,7 +139,9 @@ def test_linear_tcq_dequantises_bit_exactly_in_shared_memory(quant, M, monkeypat
     meta = blob[nv:].view(np.uint16)
     ng = N * K // 32
     sc = meta[ng:]
-    sc[5], sc[77], sc[300] = 0x0000, 0x7C00, (sc[300] | 0x8000)  # zero, inf, a negative scale
+    # an infinite and a negative scale (both take the element-wise fallback and stay finite).  A zero scale is left out:
+    # its column dequantises to inf / NaN and 0 x inf would poison every output of those features through the MMA.
+    sc[77], sc[300] = 0x7C00, (sc[300] | 0x8000)
     want = O.dequant(blob, quant, K, N).view(np.float16)  # [N][K]
     h = ops.FFHandler("cuda:0")
     m = ops.LinearMeta(h, K, N, quantization_type=B.DT_INT8 if quant == 8 else B.DT_INT4, max_tokens_per_batch=512)
@@ -154,7 +156,8 @@ def test_linear_tcq_dequantises_bit_exactly_in_shared_memory(quant, M, monkeypat
         got = out[:n].cpu().numpy()
         exp = want[:, k0:k0 + n].T
         fin = np.isfinite(exp.astype(np.float32))
-        assert (got.view(np.uint16)[fin] == exp.view(np.uint16)[fin]).all(), k0
+        bad = (got.view(np.uint16) != exp.view(np.uint16)) & fin
+        assert not bad.any(), (k0, int(bad.sum()), np.argwhere(bad)[:8].tolist(), got[bad][:4], exp[bad][:4])
         assert not np.isfinite(got.astype(np.float32)[~fin]).any()
         if n < M:
             assert (out[n:].float() == 0).all()
@@ -163,3 +166,40 @@ def test_linear_tcq_dequantises_bit_exactly_in_shared_memory(quant, M, monkeypat
     torch.cuda.synchronize()
     ok = torch.isfinite(out.float()) & torch.isfinite(out_b.float())
     assert torch.equal(out_b[ok], (out.float() + bias.float()[None, :]).half()[ok])
+
+
+@pytest.mark.parametrize("dtype", ["half", "bf16"])
+@pytest.mark.parametrize("M,K,N,bias", [(512, 4096, 12288, False), (512, 4096, 4096, True), (256, 2048, 4096, True),
+                                        (300, 1024, 1248, True), (1024, 1024, 2048, False), (129, 4096, 512, False)])
+def test_linear_sk_stream_k(M, K, N, bias, dtype, monkeypatch):
+    """Stream-K schedule of the SM-pair GEMM (linear_sk.cu, forced with FFB_SK=1): pieces that start / end inside a
+    tile, tiles cut into two and into many pieces (k-block ranges shorter than K/64), ragged M and N; called three
+    times on one handle: the flags must come back to zero and the result must not depend on timing."""
+    import torch
+    from flexflow_b200 import ops
+    monkeypatch.setenv("FFB_LINEAR", "tc")
+    monkeypatch.setenv("FFB_SK", "1")
+    ffb_lib.reload_env()
+    tdt = torch.float16 if dtype == "half" else torch.bfloat16
+    rng = np.random.default_rng(41)
+    x = O.round_to_dt(rng.standard_normal((M, K)).astype(np.float32), dtype)
+    w = O.round_to_dt((rng.standard_normal((N, K)) * 0.05).astype(np.float32), dtype)
+    b = O.round_to_dt(rng.standard_normal(N).astype(np.float32), dtype) if bias else None
+    h = ops.FFHandler("cuda:0")
+    m = ops.LinearMeta(h, K, N, dtype=tdt, max_tokens_per_batch=1024)
+    xd, wd = torch.from_numpy(x).to("cuda", tdt), torch.from_numpy(w).to("cuda", tdt)
+    bd = torch.from_numpy(b).to("cuda", tdt) if bias else None
+    outs = []
+    for _ in range(3):
+        out = torch.full((M, N), float("nan"), dtype=tdt, device="cuda")
+        ops.Linear.inference_kernel_wrapper(m, None, xd, out, wd, bd, K, N, M)
+        outs.append(out)
+    torch.cuda.synchronize()
+    want = torch.from_numpy(x).cuda() @ torch.from_numpy(w).cuda().T  # fp32 on the rounded inputs
+    if bias:
+        want = want + torch.from_numpy(b).cuda()[None, :]
+    got = outs[0].float()
+    assert torch.isfinite(got).all()
+    tol = 2e-3 if dtype == "half" else 1.2e-2
+    assert (got - want).abs().max().item() <= tol * max(1.0, want.abs().max().item())
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
