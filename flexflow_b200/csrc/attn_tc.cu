@@ -138,13 +138,13 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
                const __grid_constant__ AtcSched sched_param, T const *__restrict__ q_buf,
                QueryDesc const *__restrict__ qdesc, ffb_combined_batch_config_meta const *__restrict__ meta,
                float *__restrict__ partial, int *__restrict__ split_counter, T *__restrict__ out, int nq, int nkv,
-               int cache_len, float scale_log2, int kv_evict_first, long long *trace) {
+               int cache_len, float scale_log2, int kv_evict_first, int q_first, long long *trace) {
   using Cfg = AtcCfg<DH>;
   constexpr int KH = Cfg::KH, NBUF = Cfg::NBUF;
   constexpr uint32_t HALF = Cfg::HALF_BYTES;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t kv_full[NBUF], kv_empty[NBUF];
-  __shared__ __align__(8) uint64_t s_full[2], o_full, p_full, q_full;
+  __shared__ __align__(8) uint64_t s_full[2], o_full, p_full, q_full, q_issued;
   __shared__ float s_xch[2][ATC_NQ][TBM]; // [tile parity][column quarter][row]: partial row maxima / final row sums
   __shared__ uint32_t tmem_base_smem;
   __shared__ int s_rowlast[TBM];
@@ -207,6 +207,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
       mbar_init(&o_full, 1);
       mbar_init(&p_full, ATC_SOFTMAX_THREADS);
       mbar_init(&q_full, ATC_SOFTMAX_THREADS);
+      mbar_init(&q_issued, ATC_SOFTMAX_THREADS / 32);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(&tmK) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(&tmV) : "memory");
@@ -257,6 +258,11 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
             if (++sb == NBUF) {
               sb = 0;
               ph ^= 1u;
+            }
+            if (j == 0 && q_first) {
+              // The first Q rows are a few KB on the critical path (no QK^T without them); queued behind this CTA's
+              // 160 KB of K / V they arrive 2-3 us later.  One tile goes out, then the softmax warps' loads.
+              mbar_wait(&q_issued, 0);
             }
           }
         }
@@ -415,6 +421,12 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
       if (tid == 0) FFB_TR(2, 100);
       if (have) {
         fetch_rows(w);
+      }
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(&q_issued); // the producer holds its stream back until the first Q loads are queued ahead of it
+      }
+      if (have) {
         if (tid == 0) FFB_TR(2, 101);
         publish_rows();
       }
@@ -938,6 +950,8 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
   static bool const pdl = !(env("FFB_ATC_PDL") && env("FFB_ATC_PDL")[0] == '0');
   // K / V tiles loaded with the L2 evict-first policy (FFB_ATC_EVICT=0: default policy)
   int const kv_evict = !(env("FFB_ATC_EVICT") && env("FFB_ATC_EVICT")[0] == '0');
+  // the K / V stream waits (after its first tile) until the first segment's Q loads have been issued (FFB_ATC_QFIRST=0: no)
+  int const q_first = !(env("FFB_ATC_QFIRST") && env("FFB_ATC_QFIRST")[0] == '0');
 #define FFB_ATC(TT, DH)                                                                                              \
   do {                                                                                                               \
     size_t const smem = AtcCfg<DH>::SMEM;                                                                            \
@@ -954,7 +968,7 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
     cfg.numAttrs = pdl && h->profiling != 2 ? 1 : 0;                                                                 \
     FFB_CUDA_TRY(cudaLaunchKernelEx(&cfg, attn_tc_kernel<TT, DH>, tmK, tmV, sc, (TT const *)h->q_buf,                \
                                     (QueryDesc const *)h->qdesc, meta, h->partial, h->split_counter, (TT *)out,      \
-                                    d.num_q_heads, d.num_kv_heads, h->cache_len, scale_log2, kv_evict,               \
+                                    d.num_q_heads, d.num_kv_heads, h->cache_len, scale_log2, kv_evict, q_first,      \
                                     tracing ? trace : (long long *)nullptr));                                        \
   } while (0)
   if (d.dtype == FFB_DT_HALF) {

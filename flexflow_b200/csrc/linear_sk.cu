@@ -402,8 +402,11 @@ int linear_sk_supported(int dtype, int M, int K, int N, void const *ws, int cons
   if (e && e[0] == '1') {
     return 1;
   }
-  // whole waves of 256-wide tiles need no cut
-  return tiles % pairs != 0;
+  // Measured (profiles/README.md, M = 256 ... 1024 at the 7B shapes): the cut pays when the plain schedule's last wave
+  // is less than half full (M = 512, N = 12288: 96 tiles on 74 pairs, 49.3 -> 46.3 us); a fuller last wave, or fewer
+  // tiles than pairs (every tile cut into several pieces, each merge a trip through L2), is faster uncut.
+  long const rem = tiles % pairs;
+  return tiles > pairs && rem != 0 && 2 * rem < pairs;
 }
 
 int launch_linear_sk(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N,
