@@ -65,6 +65,8 @@ SIGNATURES = {
     "ffb_linear_create": (_i, [C.POINTER(LinearDesc), C.POINTER(_vp)]),
     "ffb_linear_destroy": (_i, [_vp]),
     "ffb_linear_forward": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp]),
+    "ffb_linear_forward_static": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "ffb_linear_static_scratch_bytes": (C.c_size_t, []),
     "ffb_comm_get_unique_id": (_i, [_vp]),
     "ffb_comm_init_rank": (_i, [_vp, _i, _i, C.POINTER(_vp)]),
     "ffb_comm_destroy": (_i, [_vp]),

@@ -171,6 +171,20 @@ int ffb_linear_destroy(ffb_linear_t h);
 int ffb_linear_forward(ffb_linear_t h, void const *in_dev, void *out_dev, void const *weight_dev,
                        void const *bias_dev, int batch, ffb_stream_t stream);
 
+/* ffb_linear_forward_static: no counterpart in the reference - added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ * out[batch][out_dim] = in[batch][in_dim] x weight[out_dim][in_dim]^T (+ bias), dense half / bf16 weights, computed
+ * by the SM-pair tcgen05 GEMM with its split-K workspace in a file-scope __device__ array: the call needs no handle
+ * and allocates nothing (no cudaMalloc / cudaFree, host or device side).  Limits: batch <= 1024, in_dim <= 16384 and
+ * % 64 == 0, out_dim <= 16384 and % 16 == 0; anything larger is rejected with FFB_ERR_INVALID.  The scratch
+ * (ffb_linear_static_scratch_bytes() = 19.4 MB) is held by every GPU that loads the library until exit and is SHARED
+ * by all calls: calls whose kernels overlap on the GPU (different streams) race; calls on one stream are safe.
+ * Results agree with ffb_linear_forward's within fp32-accumulation rounding (bit-identical where that entry point
+ * dispatches to the same kernel and schedule, e.g. 512 x 4096 x 4096). */
+int ffb_linear_forward_static(void const *in_dev, void *out_dev, void const *weight_dev, void const *bias_dev,
+                              int batch, int in_dim, int out_dim, int dtype, ffb_stream_t stream);
+size_t ffb_linear_static_scratch_bytes(void);
+
 /* ------------------------------------------------------------------------------------------
  * AllReduce parallel op.  Kernels::AllReduce::inference_kernel_wrapper
  * (src/parallel_ops/kernels/allreduce_kernels.cu:56-78): sum over TP shards of
