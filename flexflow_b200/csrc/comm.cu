@@ -105,7 +105,10 @@ void peer_setup(ffb_comm_s *c, NcclApi *api) {
   size_t const big_slice = ((kPeerBigMaxBytes / c->nranks + 1023) & ~(size_t)1023);
   size_t const big_bytes = (size_t)4 * c->nranks * big_slice;
   size_t const big_flag_bytes = ((size_t)2 * c->nranks * kPeerBigChunks * sizeof(int) + 256 + 1023) & ~(size_t)1023;
-  size_t const total = small_bytes + big_flag_bytes + big_bytes;
+  // flag-in-data area: 2 phases x nranks slots x (one slice of the largest such message, doubled by its flags)
+  size_t const ll_slice = ((2 * kPeerLLMaxBytes / c->nranks + 1023) & ~(size_t)1023);
+  size_t const ll_bytes = (size_t)2 * c->nranks * ll_slice + 1024; // + its epoch / completion counter
+  size_t const total = small_bytes + big_flag_bytes + big_bytes + ll_bytes;
   struct Rec {
     cudaIpcMemHandle_t handle;
     int ok;
@@ -144,6 +147,7 @@ void peer_setup(ffb_comm_s *c, NcclApi *api) {
     c->peer.flags[r] = (int *)((char *)base + recv_bytes);
     c->peer.big_flags[r] = (int *)((char *)base + small_bytes);
     c->peer.big[r] = (char *)base + small_bytes + big_flag_bytes;
+    c->peer.ll[r] = (char *)base + small_bytes + big_flag_bytes + big_bytes + 1024;
   }
   // second agreement: did EVERY rank map every area?
   int flag = ok ? 1 : 0;
@@ -164,6 +168,9 @@ void peer_setup(ffb_comm_s *c, NcclApi *api) {
   c->peer.big_slice_bytes = big_slice;
   c->peer.big_epoch = (int *)((char *)c->peer_local + small_bytes + (size_t)2 * c->nranks * kPeerBigChunks * sizeof(int));
   c->peer.big_done = c->peer.big_epoch + 1;
+  c->peer.ll_slice_bytes = ll_slice;
+  c->peer.ll_epoch = (int *)((char *)c->peer_local + small_bytes + big_flag_bytes + big_bytes);
+  c->peer.ll_done = c->peer.ll_epoch + 1;
   c->peer_ok = true;
 }
 

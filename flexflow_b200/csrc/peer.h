@@ -30,9 +30,17 @@ struct PeerTable {
   size_t big_slice_bytes = 0;
   int *big_epoch; // local
   int *big_done;  // local
+  // ---- the same two shots with flag-in-data lines (peer_allreduce.cu, messages up to kPeerLLMaxBytes) ----
+  // ll[p]: rank p's area [2 (phase)][nranks (source)][ll_slice_bytes] of 16-byte lines {data, epoch, data, epoch}: every
+  // 8-byte half carries its own arrival flag, so no fence and no separate flag store is needed
+  char *ll[kPeerMaxRanks];
+  size_t ll_slice_bytes = 0;
+  int *ll_epoch; // local
+  int *ll_done;  // local
 };
-constexpr int kPeerBigChunks = 128;                        // CTAs (= flag slots per source) of the large-message kernel
+constexpr int kPeerBigChunks = 592;                        // CTAs (= flag slots per source) of the large-message kernel
 constexpr size_t kPeerBigMaxBytes = (size_t)16 << 20;      // largest message: 1024 tokens x 8192 x 2 bytes
+constexpr size_t kPeerLLMaxBytes = (size_t)8 << 20;        // largest flag-in-data message (its lines take twice the bytes)
 
 } // namespace ffb
 

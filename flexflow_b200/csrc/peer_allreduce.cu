@@ -15,6 +15,7 @@
 // parity (a rank can be at most one collective ahead of the slowest one); flags hold epochs and are never reset.
 // Algorithmic NVLink volume per rank: 2 (nranks - 1) / nranks x message bytes out, the same in.
 #include <algorithm>
+#include <cstdio>
 
 #include "common.cuh"
 #include "peer.h"
@@ -24,18 +25,36 @@ namespace {
 
 constexpr int PA_THREADS = 512;
 
+#ifdef FFB_PA_TRACE_BUILD
+// nvcc -DFFB_PA_TRACE_BUILD: CTA 0 stamps %globaltimer at its phase boundaries; the host prints them every 16th launch
+__device__ long long g_pa_trace[16];
+#define PA_TR(ev)                                                    \
+  do {                                                               \
+    if (blockIdx.x == 0 && threadIdx.x == 0) {                       \
+      long long t_;                                                  \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));         \
+      g_pa_trace[ev] = t_;                                           \
+    }                                                                \
+  } while (0)
+#else
+#define PA_TR(ev) ((void)0)
+#endif
+
 __device__ __forceinline__ void st_release_sys(int *p, int v) {
   asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-__device__ __forceinline__ int ld_acquire_sys(int const *p) {
+// spin on a flag a peer writes into local memory: relaxed polls, one acquire fence once it has the epoch
+__device__ __forceinline__ void wait_flag(int const *p, int epoch) {
   int v;
-  asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
+  do {
+    asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  } while (v != epoch);
+  asm volatile("fence.acq_rel.sys;" ::: "memory");
 }
-// data written by a peer over NVLink: read it from L2 / HBM, never from a stale L1 line
+// data written by a peer over NVLink into LOCAL memory: L2 is its point of coherence, so an L1-bypassing load is enough
 __device__ __forceinline__ uint4 ld_peer_written(void const *p) {
   uint4 r;
-  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+  asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
   return r;
 }
 
@@ -55,6 +74,7 @@ peer_allreduce_kernel(PeerTable const pt, T const *in, T *out, size_t count, siz
   auto hi = [&](int s) { return min(count, (size_t)s * per + min(per, (size_t)(c + 1) * cper)); };
   size_t const coff = (size_t)c * cper * sizeof(T); // byte offset of the chunk inside a slot
 
+  PA_TR(0);
   // ---- 1. push my partial sums of every foreign slice ----
   for (int i = 1; i < N; i++) {
     int const d = (me + i) % N;
@@ -65,17 +85,21 @@ peer_allreduce_kernel(PeerTable const pt, T const *in, T *out, size_t count, siz
       dst[v] = src[v];
     }
   }
-  __threadfence_system();
+  PA_TR(1);
+  // bar.sync orders every thread's stores before the releasing threads; st.release.sys is cumulative, so one fence per
+  // destination replaces a fence.sys in each of the 512 threads (measured 7 us per phase)
   __syncthreads();
+  PA_TR(2);
   if (tid < N && tid != me) {
     st_release_sys(flag(tid, 0, me), epoch);
   }
+  PA_TR(3);
   // ---- 2. reduce my slice in rank order, keep it, push it to everybody ----
   if (tid < N && tid != me) {
-    while (ld_acquire_sys(flag(me, 0, tid)) != epoch) {
-    }
+    wait_flag(flag(me, 0, tid), epoch);
   }
   __syncthreads();
+  PA_TR(4);
   {
     size_t const a = lo(me), b = hi(me);
     for (size_t v = tid; v < (b - a) / 8; v += PA_THREADS) {
@@ -102,17 +126,18 @@ peer_allreduce_kernel(PeerTable const pt, T const *in, T *out, size_t count, siz
       }
     }
   }
-  __threadfence_system();
+  PA_TR(5);
   __syncthreads();
+  PA_TR(6);
   if (tid < N && tid != me) {
     st_release_sys(flag(tid, 1, me), epoch);
   }
   // ---- 3. collect the other ranks' result slices ----
   if (tid < N && tid != me) {
-    while (ld_acquire_sys(flag(me, 1, tid)) != epoch) {
-    }
+    wait_flag(flag(me, 1, tid), epoch);
   }
   __syncthreads();
+  PA_TR(7);
   for (int i = 1; i < N; i++) {
     int const s = (me + i) % N;
     size_t const a = lo(s), b = hi(s);
@@ -124,12 +149,118 @@ peer_allreduce_kernel(PeerTable const pt, T const *in, T *out, size_t count, siz
   }
   // the last CTA to finish closes the epoch (every CTA read it at kernel start)
   __syncthreads();
+  PA_TR(8);
   if (tid == 0) {
     int const prev = atomicAdd(pt.big_done, 1);
     if (prev == (int)gridDim.x - 1) {
       *pt.big_done = 0;
       __threadfence();
       *reinterpret_cast<int volatile *>(pt.big_epoch) = epoch;
+    }
+  }
+}
+
+// ---- flag-in-data variant (messages up to kPeerLLMaxBytes) -------------------------------------------------------
+// The flag kernel above pays, per phase, a release fence that waits for every remote store to be acknowledged plus the
+// flight of a separate flag (measured: 8 us per phase on NVLink 5 / NVSwitch whatever the message size: a 22 us
+// floor).  Here every 8 bytes on the wire are {4 bytes of data, epoch}: an 8-byte store is single-copy atomic, so the
+// receiver simply re-reads a 16-byte line until both of its halves carry this collective's epoch.  No fence, no flag
+// store, no wait between "data written" and "flag visible"; twice the bytes on the wire, which at these sizes costs
+// less than the round trips it removes.  The area is used by this kernel only (a payload word of another format could
+// look like an epoch), starts zeroed, and epochs start at 1.  Same slicing, same rank-order fp32 sum, same
+// one-rank-computes-everybody-copies rule as above: results are bit-identical to the flag kernel's and on all ranks.
+__device__ __forceinline__ void st_ll(void *p, uint32_t d0, uint32_t d1, uint32_t flag) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(d0), "r"(flag), "r"(d1), "r"(flag) : "memory");
+}
+__device__ __forceinline__ uint2 ld_ll(void const *p, uint32_t flag) {
+  uint32_t d0, f0, d1, f1;
+  do {
+    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(d0), "=r"(f0), "=r"(d1), "=r"(f1) : "l"(p) : "memory");
+  } while (f0 != flag || f1 != flag);
+  return make_uint2(d0, d1);
+}
+
+// count % 8 == 0; per / cper as in the flag kernel.  A thread moves 8 elements (16 payload bytes = two lines) at a time.
+template <typename T>
+__global__ void __launch_bounds__(PA_THREADS)
+peer_allreduce_ll_kernel(PeerTable const pt, T const *in, T *out, size_t count, size_t per, size_t cper) {
+  int const N = pt.nranks, me = pt.rank, c = blockIdx.x, tid = threadIdx.x;
+  uint32_t const epoch = (uint32_t)(*reinterpret_cast<int volatile *>(pt.ll_epoch) + 1);
+  size_t const slice_b = pt.ll_slice_bytes;
+  auto area = [&](int rank, int phase, int src) { return pt.ll[rank] + ((size_t)phase * N + src) * slice_b; };
+  auto lo = [&](int s) { return min(count, (size_t)s * per + min(per, (size_t)c * cper)); };
+  auto hi = [&](int s) { return min(count, (size_t)s * per + min(per, (size_t)(c + 1) * cper)); };
+  size_t const coff = (size_t)c * cper * sizeof(T) * 2; // byte offset of the chunk's lines inside a slot
+  PA_TR(0);
+  // ---- 1. push my partial sums of every foreign slice ----
+  for (int i = 1; i < N; i++) {
+    int const d = (me + i) % N;
+    size_t const a = lo(d), b = hi(d);
+    char *dst = area(d, 0, me) + coff;
+    uint4 const *src = reinterpret_cast<uint4 const *>(in + a);
+    for (size_t v = tid; v < (b - a) / 8; v += PA_THREADS) {
+      uint4 const u = src[v];
+      st_ll(dst + v * 32, u.x, u.y, epoch);
+      st_ll(dst + v * 32 + 16, u.z, u.w, epoch);
+    }
+  }
+  PA_TR(1);
+  // ---- 2. reduce my slice in rank order, keep it, push it to everybody ----
+  {
+    size_t const a = lo(me), b = hi(me);
+    for (size_t v = tid; v < (b - a) / 8; v += PA_THREADS) {
+      float acc[8];
+#pragma unroll
+      for (int e = 0; e < 8; e++) {
+        acc[e] = 0.f;
+      }
+      for (int s = 0; s < N; s++) {
+        uint4 u;
+        if (s == me) {
+          u = reinterpret_cast<uint4 const *>(in + a)[v];
+        } else {
+          char const *src = area(me, 0, s) + coff + v * 32;
+          uint2 const l0 = ld_ll(src, epoch), l1 = ld_ll(src + 16, epoch);
+          u = make_uint4(l0.x, l0.y, l1.x, l1.y);
+        }
+        float f[8];
+        unpack8<T>(u, f);
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+          acc[e] += f[e];
+        }
+      }
+      uint4 const r = pack8<T>(acc);
+      reinterpret_cast<uint4 *>(out + a)[v] = r;
+      for (int i = 1; i < N; i++) {
+        int const d = (me + i) % N;
+        char *dst = area(d, 1, me) + coff + v * 32;
+        st_ll(dst, r.x, r.y, epoch);
+        st_ll(dst + 16, r.z, r.w, epoch);
+      }
+    }
+  }
+  PA_TR(2);
+  // ---- 3. collect the other ranks' result slices ----
+  for (int i = 1; i < N; i++) {
+    int const s = (me + i) % N;
+    size_t const a = lo(s), b = hi(s);
+    char const *src = area(me, 1, s) + coff;
+    uint4 *dst = reinterpret_cast<uint4 *>(out + a);
+    for (size_t v = tid; v < (b - a) / 8; v += PA_THREADS) {
+      uint2 const l0 = ld_ll(src + v * 32, epoch), l1 = ld_ll(src + v * 32 + 16, epoch);
+      dst[v] = make_uint4(l0.x, l0.y, l1.x, l1.y);
+    }
+  }
+  PA_TR(3);
+  // the last CTA to finish closes the epoch (every CTA read it at kernel start)
+  __syncthreads();
+  if (tid == 0) {
+    int const prev = atomicAdd(pt.ll_done, 1);
+    if (prev == (int)gridDim.x - 1) {
+      *pt.ll_done = 0;
+      __threadfence();
+      *reinterpret_cast<int volatile *>(pt.ll_epoch) = (int)epoch;
     }
   }
 }
@@ -145,19 +276,50 @@ int launch_peer_allreduce(PeerTable const *pt, void const *in, void *out, size_t
   int const N = pt->nranks;
   // slice per rank and chunk per CTA, both multiples of 8 elements; chunks of >= 2 KiB keep the flag traffic small
   size_t const per = ((count + N - 1) / N + 7) & ~(size_t)7;
-  int grid = (int)std::min<size_t>(kPeerBigChunks, std::max<size_t>(1, per * 2 / 2048));
+  // FFB_PEER_GRID / FFB_PEER_CHUNK: experiment knobs (CTA cap, minimum chunk bytes)
+  static int const grid_cap = env("FFB_PEER_GRID") ? std::max(1, std::min(kPeerBigChunks, atoi(env("FFB_PEER_GRID")))) : 128;
+  static size_t const min_chunk = env("FFB_PEER_CHUNK") ? (size_t)std::max(256, atoi(env("FFB_PEER_CHUNK"))) : 2048;
+  int grid = (int)std::min<size_t>(grid_cap, std::max<size_t>(1, per * 2 / min_chunk));
   size_t const cper = ((per + grid - 1) / grid + 7) & ~(size_t)7;
   grid = (int)((per + cper - 1) / cper);
   if (per * 2 > pt->big_slice_bytes) {
     set_error("allreduce message of %zu elements exceeds the peer area", count);
     return FFB_ERR_INVALID;
   }
-  if (dtype == FFB_DT_HALF) {
+  // flag-in-data lines up to kPeerLLMaxBytes (FFB_PEER_LL=0: always the flag kernel)
+  static bool const ll_on = !(env("FFB_PEER_LL") && env("FFB_PEER_LL")[0] == '0');
+  bool const ll = ll_on && pt->ll_slice_bytes > 0 && count * 2 <= kPeerLLMaxBytes && per * 4 <= pt->ll_slice_bytes;
+  if (ll) {
+    // measured at 2 ranks (tools/bench_allreduce.py): two CTAs per SM up to 4 MiB (26.6 us against 28.8 with one), one above
+    static int const ll_cap_env = env("FFB_PEER_LL_GRID") ? std::max(1, std::min(kPeerBigChunks, atoi(env("FFB_PEER_LL_GRID")))) : 0;
+    int const ll_cap = ll_cap_env ? ll_cap_env : (count * 2 <= ((size_t)4 << 20) ? 2 * kNumSMs : kNumSMs);
+    grid = (int)std::min<size_t>(ll_cap, std::max<size_t>(1, per * 2 / min_chunk));
+    size_t const lcper = ((per + grid - 1) / grid + 7) & ~(size_t)7;
+    grid = (int)((per + lcper - 1) / lcper);
+    if (dtype == FFB_DT_HALF) {
+      peer_allreduce_ll_kernel<__half><<<grid, PA_THREADS, 0, s>>>(*pt, (__half const *)in, (__half *)out, count, per, lcper);
+    } else {
+      peer_allreduce_ll_kernel<__nv_bfloat16><<<grid, PA_THREADS, 0, s>>>(*pt, (__nv_bfloat16 const *)in, (__nv_bfloat16 *)out, count, per, lcper);
+    }
+  } else if (dtype == FFB_DT_HALF) {
     peer_allreduce_kernel<__half><<<grid, PA_THREADS, 0, s>>>(*pt, (__half const *)in, (__half *)out, count, per, cper);
   } else {
     peer_allreduce_kernel<__nv_bfloat16><<<grid, PA_THREADS, 0, s>>>(*pt, (__nv_bfloat16 const *)in, (__nv_bfloat16 *)out, count, per, cper);
   }
   FFB_LAUNCH_CHECK();
+#ifdef FFB_PA_TRACE_BUILD
+  static int calls = 0;
+  if (++calls % 16 == 0) {
+    long long h[16];
+    cudaStreamSynchronize(s);
+    cudaMemcpyFromSymbol(h, g_pa_trace, sizeof(h));
+    fprintf(stderr, "PATRACE rank %d count %zu grid %d:", pt->rank, count, grid);
+    for (int e = 1; e <= 8; e++) {
+      fprintf(stderr, " %lld", h[e] - h[0]);
+    }
+    fprintf(stderr, "\n");
+  }
+#endif
   return FFB_OK;
 }
 

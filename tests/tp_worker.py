@@ -104,7 +104,7 @@ def main():
         import ctypes as C
         from flexflow_b200 import batch_config as B
         from flexflow_b200 import lib as L
-        sizes = [8, 4096, 12 * 1024, 512 * 4096, 1000 * 1000, 8 * 1024 * 1024, 64 * 4096 + 8]
+        sizes = [8, 4096, 12 * 1024, 512 * 4096, 1000 * 1000, 8 * 1024 * 1024, 64 * 4096 + 8, 4 * 1024 * 1024]
         for it in range(30):
             n = sizes[it % len(sizes)]
             dt = torch.float16 if it % 2 == 0 else torch.bfloat16
@@ -122,6 +122,27 @@ def main():
                                            B.DT_HALF if dt == torch.float16 else B.DT_BF16, st), "ffb_allreduce")
             torch.cuda.synchronize()
             assert torch.equal(y.view(torch.int16), want.view(torch.int16)), "peer allreduce differs (n=%d, it=%d)" % (n, it)
+        # back-to-back collectives with no host synchronisation in between (slot reuse across epochs): x <- sum over
+        # ranks, 6 times in place; every rank must hold the same bits as a torch replay of the recurrence
+        n = 512 * 4096
+        xin = (torch.randn(n, generator=g) * 0.5).half().to(dev) * (rank + 1)
+        parts = [torch.empty_like(xin) for _ in range(world)]
+        dist.all_gather(parts, xin)
+        y = xin.clone()
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        for _ in range(6):
+            L.check(L.load().ffb_allreduce(comm._h, C.c_void_p(y.data_ptr()), C.c_void_p(y.data_ptr()), n, B.DT_HALF, st), "ffb_allreduce")
+        torch.cuda.synchronize()
+        want = parts[0].float()
+        for t in parts[1:]:
+            want = want + t.float()
+        want = want.half()
+        for _ in range(5):
+            acc = want.float()
+            for _r in range(1, world):
+                acc = acc + want.float()
+            want = acc.half()
+        assert torch.equal(y.view(torch.int16), want.view(torch.int16)), "back-to-back peer allreduce differs"
         if rank == 0:
             print("PEER_OK worst %.2e, large-message allreduce bit-exact" % worst)
     dist.barrier()
