@@ -16,6 +16,7 @@
 // Algorithmic NVLink volume per rank: 2 (nranks - 1) / nranks x message bytes out, the same in.
 #include <algorithm>
 #include <cstdio>
+#include <cstring>
 
 #include "common.cuh"
 #include "peer.h"
@@ -265,6 +266,160 @@ peer_allreduce_ll_kernel(PeerTable const pt, T const *in, T *out, size_t count, 
   }
 }
 
+// ---- 128-byte lines, one flag per line (messages that fit the flag-in-data area) -------------------------------------
+// The 8-byte lines above put twice the message on the wire, and the push rate of this store pattern tops out at
+// ~400-500 GB/s per GPU (measured), so from ~1 MiB the wire time dominates.  Here a line is 128 bytes = fifteen
+// 8-byte data words + one 8-byte flag, written by EIGHT NEIGHBOURING LANES OF ONE WARP STORE INSTRUCTION (16 bytes
+// each) and read the same way: NVLink delivers the 128-byte sector of one store instruction as a unit (the property
+// NCCL's LL128 protocol is built on), so a reader that sees the flag sees the fifteen words.  1.07x the message on the
+// wire.  Lane piece p (0..7) of line j holds payload words 15 j + 2 p and 15 j + 2 p + 1; piece 7's second word is
+// the flag (epoch | magic << 32: no stale word of the 8-byte-line format can equal it).
+constexpr unsigned long long kLL128Magic = 0xA5C3F00Dull << 32;
+
+__device__ __forceinline__ void st_l128(void *p, unsigned long long a, unsigned long long b) {
+  asm volatile("st.volatile.global.v2.u64 [%0], {%1,%2};" ::"l"(p), "l"(a), "l"(b) : "memory");
+}
+__device__ __forceinline__ void ld_l128(void const *p, unsigned long long &a, unsigned long long &b) {
+  asm volatile("ld.volatile.global.v2.u64 {%0,%1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
+// whole-warp spin: every 8-lane group re-reads its line until the group's flag (piece 7, second word) is `flag`
+__device__ __forceinline__ void ld_l128_wait(void const *p, bool valid, unsigned long long flag, unsigned long long &a,
+                                             unsigned long long &b) {
+  int const lane = threadIdx.x & 31;
+  bool ok;
+  do {
+    a = b = 0;
+    if (valid) {
+      ld_l128(p, a, b);
+    }
+    unsigned long long const f = __shfl_sync(0xffffffffu, b, lane | 7);
+    ok = !valid || f == flag;
+  } while (!__all_sync(0xffffffffu, ok));
+}
+template <typename T> __device__ __forceinline__ void unpack4(unsigned long long w, float (&f)[4]) {
+  float2 const a = DT<T>::to_f2((uint32_t)w), b = DT<T>::to_f2((uint32_t)(w >> 32));
+  f[0] = a.x;
+  f[1] = a.y;
+  f[2] = b.x;
+  f[3] = b.y;
+}
+template <typename T> __device__ __forceinline__ unsigned long long pack4(float const (&f)[4]) {
+  uint32_t const lo = DT<T>::pack(f[0], f[1]), hi = DT<T>::pack(f[2], f[3]);
+  return (unsigned long long)lo | ((unsigned long long)hi << 32);
+}
+
+// lpc = lines per chunk (a slot holds gridDim.x * lpc lines)
+template <typename T>
+__global__ void __launch_bounds__(PA_THREADS)
+peer_allreduce_l128_kernel(PeerTable const pt, T const *in, T *out, size_t count, size_t per, size_t cper, int lpc) {
+  int const N = pt.nranks, me = pt.rank, c = blockIdx.x, tid = threadIdx.x;
+  int const warp = tid >> 5, lane = tid & 31, piece = lane & 7;
+  unsigned long long const flag = (unsigned long long)(uint32_t)(*reinterpret_cast<int volatile *>(pt.ll_epoch) + 1) | kLL128Magic;
+  size_t const slice_b = pt.ll_slice_bytes;
+  auto area = [&](int rank, int phase, int src) { return pt.ll[rank] + ((size_t)phase * N + src) * slice_b + (size_t)c * lpc * 128; };
+  auto lo = [&](int s) { return min(count, (size_t)s * per + min(per, (size_t)c * cper)); };
+  auto hi = [&](int s) { return min(count, (size_t)s * per + min(per, (size_t)(c + 1) * cper)); };
+  constexpr int LPI = PA_THREADS / 8; // lines per CTA iteration
+  PA_TR(0);
+  // ---- 1. push my partial sums of every foreign slice ----
+  for (int i = 1; i < N; i++) {
+    int const d = (me + i) % N;
+    size_t const a = lo(d), b = hi(d);
+    int const nwords = (int)((b - a) / 4), nlines = (nwords + 14) / 15;
+    unsigned long long const *src = reinterpret_cast<unsigned long long const *>(in + a);
+    char *dst = area(d, 0, me);
+    for (int base = warp * 4; base < nlines; base += LPI) {
+      int const line = base + (lane >> 3);
+      if (line < nlines) {
+        int const w = line * 15 + 2 * piece;
+        unsigned long long const w0 = w < nwords ? src[w] : 0ull;
+        unsigned long long const w1 = piece == 7 ? flag : (w + 1 < nwords ? src[w + 1] : 0ull);
+        st_l128(dst + (size_t)line * 128 + piece * 16, w0, w1);
+      }
+    }
+  }
+  PA_TR(1);
+  // ---- 2. reduce my slice in rank order, keep it, push it to everybody ----
+  {
+    size_t const a = lo(me), b = hi(me);
+    int const nwords = (int)((b - a) / 4), nlines = (nwords + 14) / 15;
+    unsigned long long const *mine = reinterpret_cast<unsigned long long const *>(in + a);
+    unsigned long long *res = reinterpret_cast<unsigned long long *>(out + a);
+    for (int base = warp * 4; base < nlines; base += LPI) {
+      int const line = base + (lane >> 3);
+      bool const valid = line < nlines;
+      int const w = line * 15 + 2 * piece;
+      bool const has0 = valid && w < nwords, has1 = valid && piece != 7 && w + 1 < nwords;
+      float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int s = 0; s < N; s++) {
+        unsigned long long w0 = 0, w1 = 0;
+        if (s == me) {
+          w0 = has0 ? mine[w] : 0ull;
+          w1 = has1 ? mine[w + 1] : 0ull;
+        } else {
+          ld_l128_wait(area(me, 0, s) + (size_t)line * 128 + piece * 16, valid, flag, w0, w1);
+        }
+        float f[4];
+        unpack4<T>(w0, f);
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+          acc0[e] += f[e];
+        }
+        unpack4<T>(w1, f); // (piece 7: the flag word; its sum is never used)
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+          acc1[e] += f[e];
+        }
+      }
+      unsigned long long const r0 = pack4<T>(acc0), r1 = piece == 7 ? flag : pack4<T>(acc1);
+      if (has0) {
+        res[w] = r0;
+      }
+      if (has1) {
+        res[w + 1] = r1;
+      }
+      if (valid) {
+        for (int i = 1; i < N; i++) {
+          int const d = (me + i) % N;
+          st_l128(area(d, 1, me) + (size_t)line * 128 + piece * 16, has0 ? r0 : 0ull, piece == 7 ? flag : (has1 ? r1 : 0ull));
+        }
+      }
+    }
+  }
+  PA_TR(2);
+  // ---- 3. collect the other ranks' result slices ----
+  for (int i = 1; i < N; i++) {
+    int const s = (me + i) % N;
+    size_t const a = lo(s), b = hi(s);
+    int const nwords = (int)((b - a) / 4), nlines = (nwords + 14) / 15;
+    unsigned long long *res = reinterpret_cast<unsigned long long *>(out + a);
+    char const *src = area(me, 1, s);
+    for (int base = warp * 4; base < nlines; base += LPI) {
+      int const line = base + (lane >> 3);
+      bool const valid = line < nlines;
+      int const w = line * 15 + 2 * piece;
+      unsigned long long w0, w1;
+      ld_l128_wait(src + (size_t)line * 128 + piece * 16, valid, flag, w0, w1);
+      if (valid && w < nwords) {
+        res[w] = w0;
+      }
+      if (valid && piece != 7 && w + 1 < nwords) {
+        res[w + 1] = w1;
+      }
+    }
+  }
+  PA_TR(3);
+  __syncthreads();
+  if (tid == 0) {
+    int const prev = atomicAdd(pt.ll_done, 1);
+    if (prev == (int)gridDim.x - 1) {
+      *pt.ll_done = 0;
+      __threadfence();
+      *reinterpret_cast<int volatile *>(pt.ll_epoch) = (int)(uint32_t)flag;
+    }
+  }
+}
+
 } // namespace
 
 int peer_allreduce_supported(PeerTable const *pt, size_t count, int dtype) {
@@ -286,9 +441,28 @@ int launch_peer_allreduce(PeerTable const *pt, void const *in, void *out, size_t
     set_error("allreduce message of %zu elements exceeds the peer area", count);
     return FFB_ERR_INVALID;
   }
-  // flag-in-data lines up to kPeerLLMaxBytes (FFB_PEER_LL=0: always the flag kernel)
-  static bool const ll_on = !(env("FFB_PEER_LL") && env("FFB_PEER_LL")[0] == '0');
-  bool const ll = ll_on && pt->ll_slice_bytes > 0 && count * 2 <= kPeerLLMaxBytes && per * 4 <= pt->ll_slice_bytes;
+  // Protocol: 128-byte lines with one flag per line when the message fits the flag-in-data area (default), 8-byte
+  // lines (FFB_PEER_PROTO=ll, up to kPeerLLMaxBytes), or separate flags (FFB_PEER_PROTO=flag, and anything larger).
+  // Chosen once per process: the two line formats share the area and must not alternate.
+  static int const proto = !env("FFB_PEER_PROTO") ? 2 : (strcmp(env("FFB_PEER_PROTO"), "ll") == 0 ? 1 : (strcmp(env("FFB_PEER_PROTO"), "flag") == 0 ? 0 : 2));
+  if (proto == 2 && pt->ll_slice_bytes > 0) {
+    static int const cap_env = env("FFB_PEER_LL_GRID") ? std::max(1, std::min(kPeerBigChunks, atoi(env("FFB_PEER_LL_GRID")))) : 0;
+    int const cap = cap_env ? cap_env : (count * 2 > ((size_t)4 << 20) ? 2 * kNumSMs : kNumSMs); // measured, 2 ranks
+    int g = (int)std::min<size_t>(cap, std::max<size_t>(1, per * 2 / min_chunk));
+    size_t const lcper = ((per + g - 1) / g + 7) & ~(size_t)7;
+    g = (int)((per + lcper - 1) / lcper);
+    int const lpc = (int)((lcper / 4 + 14) / 15);
+    if ((size_t)g * lpc * 128 <= pt->ll_slice_bytes) {
+      if (dtype == FFB_DT_HALF) {
+        peer_allreduce_l128_kernel<__half><<<g, PA_THREADS, 0, s>>>(*pt, (__half const *)in, (__half *)out, count, per, lcper, lpc);
+      } else {
+        peer_allreduce_l128_kernel<__nv_bfloat16><<<g, PA_THREADS, 0, s>>>(*pt, (__nv_bfloat16 const *)in, (__nv_bfloat16 *)out, count, per, lcper, lpc);
+      }
+      FFB_LAUNCH_CHECK();
+      return FFB_OK;
+    }
+  }
+  bool const ll = proto == 1 && pt->ll_slice_bytes > 0 && count * 2 <= kPeerLLMaxBytes && per * 4 <= pt->ll_slice_bytes;
   if (ll) {
     // measured at 2 ranks (tools/bench_allreduce.py): two CTAs per SM up to 4 MiB (26.6 us against 28.8 with one), one above
     static int const ll_cap_env = env("FFB_PEER_LL_GRID") ? std::max(1, std::min(kPeerBigChunks, atoi(env("FFB_PEER_LL_GRID")))) : 0;
