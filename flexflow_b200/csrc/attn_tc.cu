@@ -827,9 +827,43 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
     return FFB_OK;
   }
   int const G = d.num_q_heads / d.num_kv_heads;
+  // The schedule depends on the batch descriptor and the handle's shape only, and every layer of a step asks for the
+  // same one: the search below (~100 candidate range lengths x a walk over all CTAs and units: 40-80 us of host time)
+  // runs once per step instead of once per layer.  Per thread, one entry.
+  struct SchedKey {
+    int nreq, nkv, G, cache_len, mode, head_dim, rg_env;
+    size_t partial_bytes;
+    AtcReq reqs[FFB_MAX_NUM_REQUESTS];
+  };
+  struct SchedCache {
+    bool valid = false;
+    SchedKey key;
+    AtcSched sc;
+    int cum = 0;
+  };
+  static thread_local SchedCache cache;
+  SchedKey key;
+  memset(&key, 0, sizeof(key));
+  key.nreq = nreq;
+  key.nkv = d.num_kv_heads;
+  key.G = G;
+  key.cache_len = h->cache_len;
+  key.mode = d.mode;
+  key.head_dim = d.head_dim;
+  key.rg_env = ffb::env("FFB_ATC_RG") ? atoi(ffb::env("FFB_ATC_RG")) : 0;
+  key.partial_bytes = h->partial_bytes;
+  bool const cacheable = nreq <= FFB_MAX_NUM_REQUESTS;
+  if (cacheable) {
+    memcpy(key.reqs, reqs, sizeof(AtcReq) * nreq);
+  }
+  bool const hit = cacheable && cache.valid && memcmp(&cache.key, &key, sizeof(key)) == 0;
   AtcSched sc;
-  sc.n_ent = 0;
   int cum = 0;
+  if (hit) {
+    sc = cache.sc;
+    cum = cache.cum;
+  } else {
+  sc.n_ent = 0;
   for (int i = 0; i < nreq; i++) {
     AtcReq const &rq = reqs[i];
     if (rq.qlen <= 0) {
@@ -927,6 +961,15 @@ int launch_attn_tc(ffb_attn_s *h, ffb_combined_batch_config_meta const *meta, vo
   }
   sc.rg = rg;
   sc.maxpieces = maxp;
+  if (cacheable) {
+    cache.key = key;
+    cache.sc = sc;
+    cache.cum = cum;
+    cache.valid = true;
+  }
+  } // !hit
+  int const rg = sc.rg, maxp = sc.maxpieces;
+  (void)maxp;
   int const grid = (cum + rg - 1) / rg;
   float const scale = d.qk_prod_scaling ? 1.0f / sqrtf((float)d.head_dim) : 1.0f;
   float const scale_log2 = scale * 1.4426950408889634f;
