@@ -229,9 +229,15 @@ linear_tcq_kernel(const __grid_constant__ CUtensorMap tmA, uint8_t const *__rest
 
 } // namespace
 
-// half activations, int8 / int4 blobs, N a multiple of the 128-wide tile, K of the 64-wide k-block
+// half activations, int8 / int4 blobs, N a multiple of the 128-wide tile, K of the 64-wide k-block.
+// OFF unless FFB_TCQ=1: measured at the 7B shapes (tools/bench_quant.py --m 128 / 512, profiles/README.md) the kernel is
+// bound by its converter warps (every 256-row M tile dequantises the whole matrix again, each lane on a dependent
+// chain of L2 reads) and loses to dequantise-to-scratch + the SM-pair GEMM: 153 against 89 us (qkv_proj, int8, 512
+// tokens), 79 against 41 us (o_proj), 76 against 70 us at 128 tokens.  Kept for the bit-exact test and as the base of
+// a version with TMA-staged codes.
 int linear_tcq_supported(int dtype, int quant, int K, int N) {
-  if (env("FFB_DISABLE_TCQ")) {
+  char const *e = env("FFB_TCQ");
+  if (!(e && e[0] == '1') || env("FFB_DISABLE_TCQ")) {
     return 0;
   }
   return dtype == FFB_DT_HALF && (quant == FFB_DT_INT8 || quant == FFB_DT_INT4) && K % Q_BK == 0 && N % Q_BN == 0;

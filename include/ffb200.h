@@ -152,9 +152,10 @@ int ffb_dequant_int8(void const *blob_dev, void *out_dev, int in_dim, int out_di
  * inference_kernel_wrapper (src/ops/kernels/linear_kernels.cu:133-140,187-195,450-582):
  * out[batch][out_dim] = in[batch][in_dim] * W^T (+ bias), W stored [out_dim][in_dim] (in fastest).
  * quant_type FFB_DT_NONE: weight_dev is DT; FFB_DT_INT8 / FFB_DT_INT4: weight_dev is the blob
- * above, dequantised on chip inside the GEMM - in registers for decode batches, in shared memory ahead of the
- * tensor-core MMA for larger ones - and never materialised in HBM (exception: bf16 group meta or out_dim not a
- * multiple of 128 at more than 64 tokens, which dequantise into a private scratch first).
+ * above.  Up to 64 tokens it is dequantised on chip inside the GEMM (in registers) and never materialised in HBM; above
+ * that it is dequantised into a private scratch of in_dim x out_dim DT elements (allocated at create when max_batch >
+ * 64) and fed to the tensor-core GEMM, as the reference does (linear_kernels.cu:464-528).  FFB_TCQ=1 selects an
+ * in-shared-memory dequantising GEMM for those batches instead (measured slower; profiles/README.md).
  * Accumulation is fp32 (the reference accumulates in DT, linear_kernels.cu:507-528).
  * ------------------------------------------------------------------------------------------ */
 typedef struct {

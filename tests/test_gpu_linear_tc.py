@@ -131,6 +131,8 @@ def test_linear_tcq_dequantises_bit_exactly_in_shared_memory(quant, M, monkeypat
     bias."""
     import torch
     from flexflow_b200 import ops
+    monkeypatch.setenv("FFB_TCQ", "1")  # off by default: slower than dequantise-to-scratch + GEMM (profiles/README.md)
+    ffb_lib.reload_env()
     K, N = 512, 256
     rng = np.random.default_rng(quant * 100 + M)
     w = (rng.standard_normal((N, K)) * 0.05).astype(np.float32)

@@ -36,7 +36,7 @@ def main():
                 continue
             nb = 6 if lname == "qkv_proj" else 16  # rotate blobs: > L2
             blobs = [make_blob(K, N, bits, gen) for _ in range(nb)]
-            m = ops.LinearMeta(h, K, N, torch.float16, qt, 64)
+            m = ops.LinearMeta(h, K, N, torch.float16, qt, max(64, M))
             x = torch.randn(M, K, device="cuda").half()
             out = torch.empty(M, N, device="cuda", dtype=torch.float16)
             i = [0]
