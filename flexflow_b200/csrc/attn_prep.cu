@@ -21,6 +21,7 @@ prep_kernel(T const *__restrict__ qkv, T *__restrict__ q_buf, T *__restrict__ k_
             int num_generation_tokens) {
   // the attention kernel that follows is launched as a programmatic dependent: let it start its set-up (and the
   // stream of K/V rows older than this batch) now; it waits for this grid before it touches anything written here
+  asm volatile("griddepcontrol.wait;" ::: "memory"); // (no-op unless launched as a programmatic dependent)
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   int const t = blockIdx.x;
   int const H = nq * DH;
@@ -243,6 +244,10 @@ static int launch_prep_t(ffb_attn_s *h, int mode, ffb_combined_batch_config_meta
   // experiment hook: FFB_PREP_CARVEOUT=<percent> asks for that shared-memory carve-out, so that a small kernel between
   // two 200 KB-shared-memory kernels does not flip the SMs' L1 / shared split twice
   static int const carve = ffb::env("FFB_PREP_CARVEOUT") ? atoi(ffb::env("FFB_PREP_CARVEOUT")) : -1;
+  // FFB_PREP_PDL=1 launches this kernel as a programmatic dependent of the projection GEMM before it.  OFF by default:
+  // measured at configs[3] the attention kernel (itself a dependent of this one, triggered at its top) then becomes
+  // resident first and its spinning warps share the SMs with this grid: prep + attention 42.8 -> 50.9 us.
+  static bool const prep_pdl = ffb::env("FFB_PREP_PDL") && atoi(ffb::env("FFB_PREP_PDL")) != 0;
 #define FFB_PREP(DH)                                                                                   \
   if (carve >= 0) {                                                                                    \
     static bool set = false;                                                                           \
@@ -251,10 +256,21 @@ static int launch_prep_t(ffb_attn_s *h, int mode, ffb_combined_batch_config_meta
       set = true;                                                                                      \
     }                                                                                                  \
   }                                                                                                    \
-  prep_kernel<T, DH><<<dim3(T_, pb), 128, 0, s>>>((T const *)qkv, (T *)h->q_buf, (T *)h->k_cache, (T *)h->v_cache, \
-                                        prev, h->qdesc, meta, mode, d.num_q_heads, d.num_kv_heads,     \
-                                        h->cache_len, d.max_requests, rp, d.scaling_query,             \
-                                        d.scaling_factor, ngen)
+  {                                                                                                    \
+    cudaLaunchConfig_t cfg = {};                                                                       \
+    cfg.gridDim = dim3(T_, pb);                                                                        \
+    cfg.blockDim = dim3(128);                                                                          \
+    cfg.stream = s;                                                                                    \
+    cudaLaunchAttribute attr[1];                                                                       \
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                                   \
+    attr[0].val.programmaticStreamSerializationAllowed = 1;                                            \
+    cfg.attrs = attr;                                                                                  \
+    cfg.numAttrs = prep_pdl ? 1 : 0;                                                                   \
+    cudaLaunchKernelEx(&cfg, prep_kernel<T, DH>, (T const *)qkv, (T *)h->q_buf, (T *)h->k_cache, (T *)h->v_cache, \
+                       (T *)prev, (QueryDesc *)h->qdesc, meta, mode, (int)d.num_q_heads, (int)d.num_kv_heads, \
+                       (int)h->cache_len, (int)d.max_requests, rp, (int)d.scaling_query, (float)d.scaling_factor, \
+                       (int)ngen);                                                                     \
+  }
   if (d.head_dim == 128) {
     FFB_PREP(128);
   } else if (d.head_dim == 64) {

@@ -194,6 +194,11 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ 
   }
   __syncthreads();
   AtcSched const &sched = s_sched;
+  if (tid == 0) {
+    // every CTA of this (single-wave) grid is resident: the next kernel of the stream - the o_proj GEMM, launched as a
+    // programmatic dependent - may start its CTAs on SMs as they free up and request its first weight tiles
+    pdl_trigger();
+  }
 
   if (warp == ATC_PRODUCER_WARP) {
     // ===== TMA producer =====  (never waits for the rest of the CTA: the stream starts at once)

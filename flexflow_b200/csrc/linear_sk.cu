@@ -140,14 +140,39 @@ linear_sk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     int m_blk = t % m_tiles, n_blk = t / m_tiles;
     int s = 0;
     uint32_t ph = 1;
+    // Launched as a programmatic dependent of the preceding kernel: the weights do not depend on it, so the W halves of
+    // the first ring fill are requested at once; the activations wait for it (griddepcontrol.wait).
+    int const pre = min(STAGES, hi - lo);
+    {
+      int pt = t, pkb = kb, pn = n_blk;
+      for (int i = 0; i < pre; i++) {
+        uint32_t const leader_full = sk_mapa(smem_u32(&full_bar[i]), 0);
+        if (rank == 0) {
+          mbar_expect_tx(&full_bar[i], 2 * (A_BYTES + B_BYTES));
+        }
+        sk_tma_load(smem_u32(sB + i * B_BYTES), &tmB, pkb * SK_BK, pn * BN + (int)rank * (BN / 2), leader_full);
+        if (++pkb == num_k) {
+          pkb = 0;
+          pt++;
+          pn = pt / m_tiles;
+        }
+      }
+    }
+    pdl_wait();
+    pdl_trigger();
     for (int pos = lo; pos < hi; pos++) {
-      mbar_wait(&empty_bar[s], ph);
+      bool const first_fill = pos - lo < pre; // (the slots of the first fill start empty; their W halves are on the way)
+      if (!first_fill) {
+        mbar_wait(&empty_bar[s], ph);
+      }
       uint32_t const leader_full = sk_mapa(smem_u32(&full_bar[s]), 0);
-      if (rank == 0) {
+      if (rank == 0 && !first_fill) {
         mbar_expect_tx(&full_bar[s], 2 * (A_BYTES + B_BYTES));
       }
       sk_tma_load(smem_u32(sA + s * A_BYTES), &tmA, kb * SK_BK, m_blk * 256 + (int)rank * SK_BM, leader_full);
-      sk_tma_load(smem_u32(sB + s * B_BYTES), &tmB, kb * SK_BK, n_blk * BN + (int)rank * (BN / 2), leader_full);
+      if (!first_fill) {
+        sk_tma_load(smem_u32(sB + s * B_BYTES), &tmB, kb * SK_BK, n_blk * BN + (int)rank * (BN / 2), leader_full);
+      }
       if (++s == STAGES) {
         s = 0;
         ph ^= 1u;
@@ -370,9 +395,18 @@ int launch_sk(void const *in, void *out, void const *w, void const *bias, int dt
   }
   FFB_SET_MAX_SMEM_ONCE(linear_sk_kernel<T>, ((size_t)225 << 10) + 1024);
   size_t const smem = (size_t)stages * stage + 16384 + 1024; // ring + epilogue staging + alignment slack
-  linear_sk_kernel<T><<<dim3(2 * P), SK_THREADS, smem, s>>>(tmA, tmB, (T *)out, (T const *)bias, M, N, K, BN, stages,
-                                                            (float4 *)ws, cnt);
-  FFB_LAUNCH_CHECK();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * P);
+  cfg.blockDim = dim3(SK_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = gemm_pdl_enabled() ? 1 : 0;
+  FFB_CUDA_TRY(cudaLaunchKernelEx(&cfg, linear_sk_kernel<T>, tmA, tmB, (T *)out, (T const *)bias, M, N, K, BN, stages,
+                                  (float4 *)ws, cnt));
   return FFB_OK;
 }
 

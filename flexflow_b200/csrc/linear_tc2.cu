@@ -172,6 +172,23 @@ linear_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // ===== TMA producer (both CTAs): this CTA's half of A and of W =====
     int it = 0; // ring item counter, runs across tiles
     T2_TR(1);
+    // Launched as a programmatic dependent of the preceding kernel: the weights do not depend on it, so the W halves of
+    // the first ring fill (k-blocks of this cluster's first unit) are requested at once; the activations wait.
+    int pre = 0;
+    if (cluster_id < units) {
+      int const t = cluster_id / S, ks = unit_slice(cluster_id, S);
+      int const n_blk = t / m_tiles, kb0 = ks * num_k / S;
+      pre = min(STAGES, (ks + 1) * num_k / S - kb0);
+      for (int i = 0; i < pre; i++) {
+        uint32_t const leader_full = mapa_u32(smem_u32(&full_bar[i]), 0);
+        if (rank == 0) {
+          mbar_expect_tx(&full_bar[i], 2 * (A_BYTES + B_BYTES));
+        }
+        tma_load_2d_2sm(smem_u32(sB + i * B_BYTES), &tmB, (kb0 + i) * T2_BK, n_blk * BN + (int)rank * (BN / 2), leader_full);
+      }
+    }
+    pdl_wait();
+    pdl_trigger();
     for (int u = cluster_id; u < units; u += num_clusters) {
       int const t = u / S, ks = unit_slice(u, S);
       int const m_blk = t % m_tiles, n_blk = t / m_tiles;
@@ -179,13 +196,18 @@ linear_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       for (int kb = ks * num_k / S; kb < kb1; kb++, it++) {
         int const s = it % STAGES;
         uint32_t const ph = (it / STAGES) & 1;
-        mbar_wait(&empty_bar[s], ph ^ 1);
+        bool const first_fill = it < pre;
         uint32_t const leader_full = mapa_u32(smem_u32(&full_bar[s]), 0);
-        if (rank == 0) {
-          mbar_expect_tx(&full_bar[s], 2 * (A_BYTES + B_BYTES));
+        if (!first_fill) {
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          if (rank == 0) {
+            mbar_expect_tx(&full_bar[s], 2 * (A_BYTES + B_BYTES));
+          }
         }
         tma_load_2d_2sm(smem_u32(sA + s * A_BYTES), &tmA, kb * T2_BK, m_blk * 256 + (int)rank * T2_BM, leader_full);
-        tma_load_2d_2sm(smem_u32(sB + s * B_BYTES), &tmB, kb * T2_BK, n_blk * BN + (int)rank * (BN / 2), leader_full);
+        if (!first_fill) {
+          tma_load_2d_2sm(smem_u32(sB + s * B_BYTES), &tmB, kb * T2_BK, n_blk * BN + (int)rank * (BN / 2), leader_full);
+        }
       }
     }
     T2_TR(2);
@@ -413,9 +435,18 @@ int launch_one(void const *in, void *out, void const *w, void const *bias, int d
   size_t const smem = (size_t)stages * stage + 16384 + 1024; // ring + epilogue staging + alignment slack
   int const tiles = ((N + BN - 1) / BN) * ((M + 255) / 256);
   dim3 grid(2 * std::min(tiles * S, kNumSMs / 2));
-  linear_tc2_kernel<T><<<grid, T2_THREADS, smem, s>>>(tmA, tmB, (T *)out, (T const *)bias, M, N, K, BN, stages, S,
-                                                      (float4 *)ws, cnt);
-  FFB_LAUNCH_CHECK();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(T2_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = gemm_pdl_enabled() ? 1 : 0;
+  FFB_CUDA_TRY(cudaLaunchKernelEx(&cfg, linear_tc2_kernel<T>, tmA, tmB, (T *)out, (T const *)bias, M, N, K, BN, stages, S,
+                                  (float4 *)ws, cnt));
 #ifdef FFB_TC2_TRACE_BUILD
   static int calls = 0;
   cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;

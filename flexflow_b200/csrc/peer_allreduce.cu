@@ -311,7 +311,15 @@ template <typename T> __device__ __forceinline__ unsigned long long pack4(float 
 // lpc = lines per chunk (a slot holds gridDim.x * lpc lines)
 template <typename T>
 __global__ void __launch_bounds__(PA_THREADS)
-peer_allreduce_l128_kernel(PeerTable const pt, T const *in, T *out, size_t count, size_t per, size_t cper, int lpc) {
+peer_allreduce_l128_kernel(PeerTable const pt, T const *in, T *out, size_t count, size_t per, size_t cper, int lpc,
+                           int trigger) {
+  // Launched as a programmatic dependent of the kernel that produced `in` (and of the previous collective, whose epoch
+  // is read below): wait for it before anything else.  Then let the next kernel of the stream - the next layer's
+  // GEMM - start its prologue and weight prefetch beside this one.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (trigger) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  }
   int const N = pt.nranks, me = pt.rank, c = blockIdx.x, tid = threadIdx.x;
   int const warp = tid >> 5, lane = tid & 31, piece = lane & 7;
   unsigned long long const flag = (unsigned long long)(uint32_t)(*reinterpret_cast<int volatile *>(pt.ll_epoch) + 1) | kLL128Magic;
@@ -453,10 +461,23 @@ int launch_peer_allreduce(PeerTable const *pt, void const *in, void *out, size_t
     g = (int)((per + lcper - 1) / lcper);
     int const lpc = (int)((lcper / 4 + 14) / 15);
     if ((size_t)g * lpc * 128 <= pt->ll_slice_bytes) {
+      // FFB_AR_PDL: bit 0 = launch as a programmatic dependent, bit 1 = trigger the next kernel early
+      static int const ar_pdl = env("FFB_AR_PDL") ? atoi(env("FFB_AR_PDL")) : 3;
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(g);
+      cfg.blockDim = dim3(PA_THREADS);
+      cfg.stream = s;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[0].val.programmaticStreamSerializationAllowed = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = (ar_pdl & 1) ? 1 : 0;
       if (dtype == FFB_DT_HALF) {
-        peer_allreduce_l128_kernel<__half><<<g, PA_THREADS, 0, s>>>(*pt, (__half const *)in, (__half *)out, count, per, lcper, lpc);
+        FFB_CUDA_TRY(cudaLaunchKernelEx(&cfg, peer_allreduce_l128_kernel<__half>, *pt, (__half const *)in, (__half *)out, count, per,
+                                        lcper, lpc, (ar_pdl >> 1) & 1));
       } else {
-        peer_allreduce_l128_kernel<__nv_bfloat16><<<g, PA_THREADS, 0, s>>>(*pt, (__nv_bfloat16 const *)in, (__nv_bfloat16 *)out, count, per, lcper, lpc);
+        FFB_CUDA_TRY(cudaLaunchKernelEx(&cfg, peer_allreduce_l128_kernel<__nv_bfloat16>, *pt, (__nv_bfloat16 const *)in,
+                                        (__nv_bfloat16 *)out, count, per, lcper, lpc, (ar_pdl >> 1) & 1));
       }
       FFB_LAUNCH_CHECK();
       return FFB_OK;

@@ -43,6 +43,15 @@ __device__ __forceinline__ void tma_load_2d_hint(void *dst, CUtensorMap const *t
   asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;"
                ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy) : "memory");
 }
+// FFB_GEMM_PDL=0: the SM-pair GEMMs are launched the ordinary way (A/B runs)
+inline bool gemm_pdl_enabled() {
+  static bool const on = !(ffb::env("FFB_GEMM_PDL") && ffb::env("FFB_GEMM_PDL")[0] == '0');
+  return on;
+}
+// programmatic dependent launch: wait for the preceding kernel of the stream (a no-op when this kernel was launched the
+// ordinary way) / let the next kernel of the stream start its prologue
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint64_t *bar) {
