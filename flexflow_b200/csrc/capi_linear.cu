@@ -26,6 +26,11 @@ int launch_linear_gemv_allreduce(PeerTable const *pt, int dtype, void const *in,
 int linear_tc_supported(int dtype, int quant, int K, int N);
 int launch_linear_tc(struct LinearTcState *st, int dtype, int quant, void const *in, void *out, void const *w,
                      void const *bias, int M, int K, int N, cudaStream_t s);
+// quantised weights, <= 64 tokens: TMA stream + in-shared-memory dequantisation + tcgen05 (linear_qtc.cu)
+int linear_qtc_supported(int dtype, int quant, int M, int K, int N);
+size_t linear_qtc_ws_bytes();
+int launch_linear_qtc(int quant, void const *in, void *out, void const *blob, void const *bias, int M, int K, int N,
+                      void *ws, cudaStream_t s);
 struct LinearTcState *linear_tc_create(int dtype, int quant, int K, int N, int max_batch);
 void linear_tc_destroy(struct LinearTcState *st);
 } // namespace ffb
@@ -33,6 +38,7 @@ void linear_tc_destroy(struct LinearTcState *st);
 struct ffb_linear_s {
   ffb_linear_desc d;
   ffb::LinearTcState *tc = nullptr;
+  void *qtc_ws = nullptr; // quantised layers: partial slots + flags of linear_qtc.cu
 };
 
 using namespace ffb;
@@ -66,12 +72,22 @@ int ffb_linear_create(ffb_linear_desc const *desc, ffb_linear_t *out) {
       return FFB_ERR_CUDA;
     }
   }
+  if (d.quant_type != FFB_DT_NONE && linear_qtc_supported(d.dtype, d.quant_type, 1, d.in_dim, d.out_dim)) {
+    if (cudaMalloc(&h->qtc_ws, linear_qtc_ws_bytes()) != cudaSuccess || cudaMemset(h->qtc_ws, 0, linear_qtc_ws_bytes()) != cudaSuccess) {
+      set_error("cudaMalloc of the quantised-projection workspace failed: %s", cudaGetErrorString(cudaGetLastError()));
+      ffb_linear_destroy(h);
+      return FFB_ERR_CUDA;
+    }
+  }
   *out = h;
   return FFB_OK;
 }
 
 int ffb_linear_destroy(ffb_linear_t h) {
   if (h) {
+    if (h->qtc_ws) {
+      cudaFree(h->qtc_ws);
+    }
     if (h->tc) {
       linear_tc_destroy(h->tc);
     }
@@ -109,6 +125,14 @@ int ffb_linear_forward(ffb_linear_t h, void const *in, void *out, void const *w,
     return launch_linear_tc(h->tc, d.dtype, d.quant_type, in, out, w, bias, batch, d.in_dim, d.out_dim, s);
   }
   bool const force_stream = force && strcmp(force, "stream") == 0;
+  if (force && strcmp(force, "qtc") == 0) { // (tests: fail instead of silently taking another kernel)
+    FFB_REQUIRE(h->qtc_ws && linear_qtc_supported(d.dtype, d.quant_type, batch, d.in_dim, d.out_dim),
+                "FFB_LINEAR=qtc but linear_qtc does not support this shape / batch");
+  }
+  if (!force_stream && !(force && strcmp(force, "qgemv") == 0) && h->qtc_ws &&
+      linear_qtc_supported(d.dtype, d.quant_type, batch, d.in_dim, d.out_dim)) {
+    return launch_linear_qtc(d.quant_type, in, out, w, bias, batch, d.in_dim, d.out_dim, h->qtc_ws, s);
+  }
   if (!force_stream && linear_gemv_supported(d.quant_type, batch, d.in_dim, d.out_dim)) {
     return launch_linear_gemv(d.dtype, in, out, w, bias, batch, d.in_dim, d.out_dim, s);
   }

@@ -264,7 +264,14 @@ linear_qgemv_kernel(__half const *__restrict__ A, uint8_t const *__restrict__ W,
               m2 = ((v >> 12) & 0xFu) | kDqMagic;
               m3 = ((v >> 8) & 0xFu) | kDqMagic;
             }
+#if defined(QG_EXP_NO_MMA) // experiment builds (tools/build_variant.sh): where does the time go
+            acc[nt][0] += __uint_as_float(dq_pair(m0, m1, c01) ^ a0);
+            acc[nt][1] += __uint_as_float(dq_pair(m2, m3, c23) ^ a1);
+#elif defined(QG_EXP_NO_DQ)
+            qg_mma(acc[nt], a0, a1, a2, a3, m0 ^ m1, m2 ^ m3);
+#else
             qg_mma(acc[nt], a0, a1, a2, a3, dq_pair(m0, m1, c01), dq_pair(m2, m3, c23));
+#endif
           }
         }
       } else { // a zero scale somewhere in this stage: element-wise rule with the raw scales (out of line)

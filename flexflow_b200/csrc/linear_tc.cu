@@ -171,6 +171,56 @@ int make_tensor_map_2d(CUtensorMap *tm, int dtype, void const *ptr, long rows, i
   return FFB_OK;
 }
 
+// [rows][row_bytes] row-major byte matrix (quantised codes), box = box_bytes x box_rows, no swizzle
+int make_tensor_map_u8(CUtensorMap *tm, void const *ptr, long rows, long row_bytes, int box_rows, int box_bytes) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled is not available from the driver");
+    return FFB_ERR_CUDA;
+  }
+  cuuint64_t gdim[2] = {(cuuint64_t)row_bytes, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)row_bytes};
+  cuuint32_t box[2] = {(cuuint32_t)box_bytes, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, (void *)ptr, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled (uint8) failed with CUresult %d (ptr %p rows %ld row bytes %ld)", (int)r, ptr, rows, row_bytes);
+    return FFB_ERR_CUDA;
+  }
+  return FFB_OK;
+}
+
+// general form: `rank` dimensions, fastest first; strides in bytes for dimensions 1 .. rank - 1; elem: 1 = uint8,
+// 2 = 16-bit (uint16 when !is_half, fp16 otherwise); swizzle128 selects the 128-byte swizzle (else none)
+int make_tensor_map_nd(CUtensorMap *tm, int elem, bool is_half, int rank, void const *ptr, unsigned long long const *dims,
+                       unsigned long long const *strides, unsigned const *box, bool swizzle128) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled is not available from the driver");
+    return FFB_ERR_CUDA;
+  }
+  cuuint64_t gdim[5], gstride[4];
+  cuuint32_t bx[5], estr[5];
+  for (int i = 0; i < rank; i++) {
+    gdim[i] = dims[i];
+    bx[i] = box[i];
+    estr[i] = 1;
+    if (i > 0) {
+      gstride[i - 1] = strides[i - 1];
+    }
+  }
+  CUtensorMapDataType const dt = elem == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
+                                           : (is_half ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_UINT16);
+  CUresult r = fn(tm, dt, rank, (void *)ptr, gdim, gstride, bx, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled (rank %d) failed with CUresult %d (ptr %p)", rank, (int)r, ptr);
+    return FFB_ERR_CUDA;
+  }
+  return FFB_OK;
+}
 
 int linear_tc2_supported(int dtype, int M, int K, int N);
 // linear_tcq.cu: quantised weights dequantised in shared memory ahead of the MMA (half activations)

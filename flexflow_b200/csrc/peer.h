@@ -40,7 +40,7 @@ struct PeerTable {
 };
 constexpr int kPeerBigChunks = 592;                        // CTAs (= flag slots per source) of the large-message kernel
 constexpr size_t kPeerBigMaxBytes = (size_t)16 << 20;      // largest message: 1024 tokens x 8192 x 2 bytes
-constexpr size_t kPeerLLMaxBytes = (size_t)8 << 20;        // largest flag-in-data message (its lines take twice the bytes)
+constexpr size_t kPeerLLMaxBytes = (size_t)16 << 20;       // largest flag-in-data message (its lines take twice the bytes)
 
 } // namespace ffb
 

@@ -29,6 +29,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
       "DONE:\n\t"
       "}" ::"r"(addr), "r"(parity) : "memory");
 }
+// the same with a suspend-time hint: the warp sleeps in the try_wait (woken when the phase completes) instead of
+// re-issuing poll / branch instructions that compete with the warps doing work
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t *bar, uint32_t parity) {
+  uint32_t const addr = smem_u32(bar);
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
+      "@p bra DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "DONE:\n\t"
+      "}" ::"r"(addr), "r"(parity), "r"(0x989680u) : "memory");
+}
 // 1-D bulk copy global -> shared (16-byte aligned, size a multiple of 16), completion counted on `bar`
 __device__ __forceinline__ void bulk_load_1d(void *dst, void const *src, uint32_t bytes, uint64_t *bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -39,6 +53,10 @@ __device__ __forceinline__ void tma_load_2d(void *dst, CUtensorMap const *tm, in
                ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
 }
 // the same with an L2 cache policy (createpolicy...) attached to the load
+__device__ __forceinline__ void tma_load_3d(void *dst, CUtensorMap const *tm, int c0, int c1, int c2, uint64_t *bar) {
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+               ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
 __device__ __forceinline__ void tma_load_2d_hint(void *dst, CUtensorMap const *tm, int c0, int c1, uint64_t *bar, uint64_t policy) {
   asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;"
                ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy) : "memory");

@@ -35,6 +35,8 @@ def main():
             if only and name != only:
                 continue
             nb = 6 if lname == "qkv_proj" else 16  # rotate blobs: > L2
+            if os.environ.get("BENCH_QUANT_NB"):
+                nb = int(os.environ["BENCH_QUANT_NB"])
             blobs = [make_blob(K, N, bits, gen) for _ in range(nb)]
             m = ops.LinearMeta(h, K, N, torch.float16, qt, max(64, M))
             x = torch.randn(M, K, device="cuda").half()
