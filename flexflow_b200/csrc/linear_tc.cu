@@ -236,6 +236,9 @@ int launch_linear_tc2(int dtype, void const *in, void *out, void const *w, void 
 int linear_sk_supported(int dtype, int M, int K, int N, void const *ws, int const *cnt);
 int launch_linear_sk(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N,
                      void *ws, int *cnt, cudaStream_t s);
+// linear_w512.cu: 256 x 512 tiles per SM pair (two UMMAs per k-step against one A tile), one wave
+int linear_w512_supported(int dtype, int M, int K, int N);
+int launch_linear_w512(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N, cudaStream_t s);
 size_t linear_tc2_ws_bytes();
 size_t linear_tc2_cnt_bytes();
 
@@ -319,6 +322,9 @@ int launch_linear_tc(LinearTcState *st, int dtype, int quant, void const *in, vo
   // M > 128 (or an N the 128-wide 1-SM tiles do not divide): SM-pair tiles (linear_tc2.cu)
   if (M > 128 && linear_tc4_supported(dtype, M, K, N)) {
     return launch_linear_tc4(dtype, in, out, wd, bias, M, K, N, s);
+  }
+  if (linear_w512_supported(dtype, M, K, N)) {
+    return launch_linear_w512(dtype, in, out, wd, bias, M, K, N, s);
   }
   if (linear_sk_supported(dtype, M, K, N, st->splitk_ws, st->splitk_cnt)) {
     return launch_linear_sk(dtype, in, out, wd, bias, M, K, N, st->splitk_ws, st->splitk_cnt, s);

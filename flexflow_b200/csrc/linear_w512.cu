@@ -1,0 +1,283 @@
+// linear_w512.cu — the SM-pair (cta_group::2) tcgen05 / TMA projection GEMM with 256 x 512 output tiles.
+// Replaces the cublasGemmEx call of Kernels::Linear::forward_kernel (src/ops/kernels/linear_kernels.cu:507-528) for
+// batched prompt / tree tokens where it applies: out[M][N] = A[M][K] * W[N][K]^T, both operands K-major, fp32 accumulation.
+//
+// Why: linear_tc2 / linear_sk (256 x 256 tiles) sit exactly on the L2 -> SM fabric limit: M = 512, N = 12288 moves
+// 402 MB of operands at the measured ~8.8 TB/s = 45.7 us, and the kernels take 46-48 us; fewer pairs do not change the
+// total (profiles/README.md).  Only fewer operand bytes per flop help.  Here a pair owns a 256 x 512 tile: per k-block
+// each CTA loads its 128 rows of A and 2 x 128 rows of W, and the leader issues TWO UMMA 256 x 256 x 16 per k-step (column
+// halves 0-255 and 256-511 of the tile) against the same A tile: 96 KB per 2 x 256 x 256 x 64 flops instead of 128 KB
+// (302 MB for the shape above).  The accumulator takes all 512 tensor-memory columns of both CTAs, so it is single-
+// buffered (the epilogue of a tile does not overlap the next tile's main loop); the kernel is selected when all tiles
+// fit ONE wave of SM pairs and fill most of it (M = 512, N = 12288: 48 tiles on 74 pairs).
+#include <algorithm>
+#include <cstdio>
+#include <type_traits>
+
+#include "tc_common.cuh"
+
+namespace ffb {
+using namespace tc;
+namespace {
+
+constexpr int W5_BM = 128, W5_BK = 64, W5_BN = 512, W5_THREADS = 256, W5_STAGES = 4;
+constexpr uint32_t W5_A_BYTES = W5_BM * W5_BK * 2;  // this CTA's 128 rows of A
+constexpr uint32_t W5_B_BYTES = 128 * W5_BK * 2;    // this CTA's 128 rows of one column half of the tile
+constexpr uint32_t W5_STAGE = W5_A_BYTES + 2 * W5_B_BYTES;
+constexpr size_t W5_SMEM = (size_t)W5_STAGES * W5_STAGE + 16384 + 1024;
+
+__device__ __forceinline__ uint32_t w5_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t w5_mapa(uint32_t local, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void w5_tma_load(uint32_t dst, CUtensorMap const *tm, int c0, int c1, uint32_t leader_bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(tm), "r"(leader_bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void w5_mma(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void w5_commit(uint64_t *bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+
+template <typename T>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(W5_THREADS, 1)
+linear_w512_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                   T *__restrict__ out, T const *__restrict__ bias, int M, int N, int K) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[W5_STAGES], empty_bar[W5_STAGES], tmem_full_bar, tmem_empty_bar;
+  __shared__ uint32_t tmem_base_smem;
+  uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t *stage_out = smem + W5_STAGES * W5_STAGE; // 4 epilogue warps x 4 KB
+
+  int const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint32_t const rank = w5_ctarank(); // 0 = leader
+  int const num_k = K / W5_BK;
+  int const m_tiles = (M + 255) / 256, n_tiles = N / W5_BN, tiles = m_tiles * n_tiles;
+  int const pair = blockIdx.x >> 1, P = gridDim.x >> 1;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < W5_STAGES; s++) {
+      mbar_init(&full_bar[s], 1);  // leader's own arrive.expect_tx; bytes arrive from both CTAs' TMA loads
+      mbar_init(&empty_bar[s], 1); // multicast tcgen05.commit
+    }
+    mbar_init(&tmem_full_bar, 1);  // multicast tcgen05.commit
+    mbar_init(&tmem_empty_bar, 8); // (leader's copy is used) one arrive per epilogue warp of both CTAs
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) { // the whole tensor memory of both CTAs: one 256 x 512 fp32 accumulator
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "r"(512u));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::);
+  }
+  tc_fence_before();
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+  tc_fence_after();
+  uint32_t const tmem_base = tmem_base_smem;
+
+  if (warp == 0 && lane == 0) {
+    // ===== TMA producer (both CTAs): this CTA's half of A and of both W column halves =====
+    int it = 0;
+    // programmatic dependent launch: the weights do not depend on the preceding kernel
+    int pre = 0;
+    if (pair < tiles) {
+      int const n_blk = pair / m_tiles;
+      pre = min(W5_STAGES, num_k);
+      for (int i = 0; i < pre; i++) {
+        uint32_t const leader_full = w5_mapa(smem_u32(&full_bar[i]), 0);
+        if (rank == 0) {
+          mbar_expect_tx(&full_bar[i], 2 * W5_STAGE);
+        }
+        uint32_t const sb = smem_u32(smem + i * W5_STAGE + W5_A_BYTES);
+        w5_tma_load(sb, &tmB, i * W5_BK, n_blk * W5_BN + (int)rank * 128, leader_full);
+        w5_tma_load(sb + W5_B_BYTES, &tmB, i * W5_BK, n_blk * W5_BN + 256 + (int)rank * 128, leader_full);
+      }
+    }
+    pdl_wait();
+    pdl_trigger();
+    for (int t = pair; t < tiles; t += P) {
+      int const m_blk = t % m_tiles, n_blk = t / m_tiles;
+      for (int kb = 0; kb < num_k; kb++, it++) {
+        int const s = it % W5_STAGES;
+        uint32_t const ph = (it / W5_STAGES) & 1;
+        bool const first_fill = it < pre;
+        uint32_t const leader_full = w5_mapa(smem_u32(&full_bar[s]), 0);
+        uint32_t const sa = smem_u32(smem + s * W5_STAGE);
+        if (!first_fill) {
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          if (rank == 0) {
+            mbar_expect_tx(&full_bar[s], 2 * W5_STAGE);
+          }
+        }
+        w5_tma_load(sa, &tmA, kb * W5_BK, m_blk * 256 + (int)rank * W5_BM, leader_full);
+        if (!first_fill) {
+          w5_tma_load(sa + W5_A_BYTES, &tmB, kb * W5_BK, n_blk * W5_BN + (int)rank * 128, leader_full);
+          w5_tma_load(sa + W5_A_BYTES + W5_B_BYTES, &tmB, kb * W5_BK, n_blk * W5_BN + 256 + (int)rank * 128, leader_full);
+        }
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    if (rank == 0) {
+      // ===== MMA issuer (leader CTA only): two UMMA 256 x 256 x 16 per k-step =====
+      constexpr uint32_t fmt = std::is_same<T, __nv_bfloat16>::value ? 1u : 0u;
+      constexpr uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+      int it = 0, i = 0;
+      for (int t = pair; t < tiles; t += P, i++) {
+        mbar_wait(&tmem_empty_bar, (i & 1) ^ 1); // both CTAs' epilogues have drained the accumulator
+        tc_fence_after();
+        for (int kb = 0; kb < num_k; kb++, it++) {
+          int const s = it % W5_STAGES;
+          mbar_wait(&full_bar[s], (it / W5_STAGES) & 1);
+          tc_fence_after();
+          uint32_t const sa = smem_u32(smem + s * W5_STAGE);
+          uint64_t const da = umma_desc_sw128(sa);
+          uint64_t const db0 = umma_desc_sw128(sa + W5_A_BYTES), db1 = umma_desc_sw128(sa + W5_A_BYTES + W5_B_BYTES);
+#pragma unroll
+          for (int k = 0; k < W5_BK / 16; k++) {
+            w5_mma(tmem_base, da + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+            w5_mma(tmem_base + 256u, da + (uint64_t)(k * 2), db1 + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+          }
+          w5_commit(&empty_bar[s]);
+        }
+        w5_commit(&tmem_full_bar);
+      }
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue (both CTAs): this CTA's 128 x 512 half of the accumulator =====
+    int const q = warp & 3;
+    uint8_t *const stg = stage_out + (warp - 4) * 4096;
+    int i = 0;
+    for (int t = pair; t < tiles; t += P, i++) {
+      int const m_blk = t % m_tiles, n_blk = t / m_tiles;
+      mbar_wait(&tmem_full_bar, i & 1);
+      tc_fence_after();
+      int const row0 = m_blk * 256 + (int)rank * W5_BM + q * 32, col0 = n_blk * W5_BN;
+      uint32_t const tsrc = tmem_base + ((uint32_t)(q * 32) << 16);
+      uint32_t ra[32], rb[32];
+      tmem_ld32_nowait(tsrc, ra);
+      tmem_ld32_nowait(tsrc + 32u, rb);
+#pragma unroll 1
+      for (int c0 = 0; c0 < W5_BN; c0 += 64) {
+        tmem_ld_wait32(ra);
+        reg_tie32(rb);
+        T const *const bp = bias ? bias + col0 + c0 : nullptr;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+          float f[8];
+#pragma unroll
+          for (int e = 0; e < 8; e++) {
+            f[e] = __uint_as_float(j < 4 ? ra[j * 8 + e] : rb[(j - 4) * 8 + e]);
+          }
+          if (bp) {
+#pragma unroll
+            for (int e = 0; e < 8; e++) {
+              f[e] += DT<T>::to_f(bp[j * 8 + e]);
+            }
+          }
+          *reinterpret_cast<uint4 *>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) = pack8<T>(f);
+        }
+        if (c0 + 64 < W5_BN) {
+          tmem_ld32_nowait(tsrc + (uint32_t)(c0 + 64), ra);
+          tmem_ld32_nowait(tsrc + (uint32_t)(c0 + 96), rb);
+        }
+        __syncwarp();
+        int const j = lane & 7, gcol = col0 + c0 + j * 8;
+#pragma unroll
+        for (int ii = 0; ii < 8; ii++) {
+          int const r = ii * 4 + (lane >> 3);
+          uint4 const v = *reinterpret_cast<uint4 const *>(stg + r * 128 + ((j ^ (r & 7)) << 4));
+          if (row0 + r < M) {
+            *reinterpret_cast<uint4 *>(out + (size_t)(row0 + r) * N + gcol) = v;
+          }
+        }
+        __syncwarp();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        uint32_t const remote = w5_mapa(smem_u32(&tmem_empty_bar), 0);
+        asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+      }
+    }
+  }
+  tc_fence_before();
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u));
+  }
+}
+
+template <typename T>
+int launch_w5(void const *in, void *out, void const *w, void const *bias, int dtype, int M, int K, int N, cudaStream_t s) {
+  CUtensorMap tmA, tmB;
+  int rc = make_tensor_map_2d(&tmA, dtype, in, M, K, W5_BM);
+  if (rc != FFB_OK) {
+    return rc;
+  }
+  rc = make_tensor_map_2d(&tmB, dtype, w, N, K, 128);
+  if (rc != FFB_OK) {
+    return rc;
+  }
+  FFB_SET_MAX_SMEM_ONCE(linear_w512_kernel<T>, W5_SMEM);
+  int const tiles = ((M + 255) / 256) * (N / W5_BN);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * std::min(tiles, kNumSMs / 2));
+  cfg.blockDim = dim3(W5_THREADS);
+  cfg.dynamicSmemBytes = W5_SMEM;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = gemm_pdl_enabled() ? 1 : 0;
+  FFB_CUDA_TRY(cudaLaunchKernelEx(&cfg, linear_w512_kernel<T>, tmA, tmB, (T *)out, (T const *)bias, M, N, K));
+  return FFB_OK;
+}
+
+} // namespace
+
+// one wave of 256 x 512 tiles that fills at least 60 % of the SM pairs; FFB_W512=0 disables, =1 forces (any tile count)
+int linear_w512_supported(int dtype, int M, int K, int N) {
+  char const *e = env("FFB_W512");
+  if (e && e[0] == '0') {
+    return 0;
+  }
+  if (!(dtype == FFB_DT_HALF || dtype == FFB_DT_BF16) || M <= 128 || K % W5_BK != 0 || N % W5_BN != 0) {
+    return 0;
+  }
+  if (e && e[0] == '1') {
+    return 1;
+  }
+  int const tiles = ((M + 255) / 256) * (N / W5_BN), pairs = kNumSMs / 2;
+  return tiles <= pairs && 10 * tiles >= 6 * pairs;
+}
+
+int launch_linear_w512(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N,
+                       cudaStream_t s) {
+  if (dtype == FFB_DT_HALF) {
+    return launch_w5<__half>(in, out, w, bias, dtype, M, K, N, s);
+  }
+  return launch_w5<__nv_bfloat16>(in, out, w, bias, dtype, M, K, N, s);
+}
+
+} // namespace ffb

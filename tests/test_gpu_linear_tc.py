@@ -205,3 +205,38 @@ def test_linear_sk_stream_k(M, K, N, bias, dtype, monkeypatch):
     tol = 2e-3 if dtype == "half" else 1.2e-2
     assert (got - want).abs().max().item() <= tol * max(1.0, want.abs().max().item())
     assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+
+
+@pytest.mark.parametrize("dtype", ["half", "bf16"])
+@pytest.mark.parametrize("M,K,N,bias", [(512, 4096, 12288, False), (300, 1024, 1024, True), (1024, 1024, 2048, True),
+                                        (1024, 512, 20480, False), (129, 2048, 512, True)])
+def test_linear_w512_tiles(M, K, N, bias, dtype, monkeypatch):
+    """256 x 512 tiles per SM pair (linear_w512.cu, forced with FFB_W512=1): two UMMAs per k-step against one A tile,
+    single-buffered 512-column accumulator; ragged M, several tiles per pair (160 tiles on 74 pairs: the accumulator
+    hand-over between tiles), the programmatic-dependent-launch prologue on back-to-back calls."""
+    import torch
+    from flexflow_b200 import ops
+    monkeypatch.setenv("FFB_LINEAR", "tc")
+    monkeypatch.setenv("FFB_W512", "1")
+    ffb_lib.reload_env()
+    tdt = torch.float16 if dtype == "half" else torch.bfloat16
+    g = torch.Generator(device="cuda").manual_seed(43)
+    x = torch.randn(M, K, generator=g, device="cuda").to(tdt)
+    w = (torch.randn(N, K, generator=g, device="cuda") * 0.05).to(tdt)
+    b = torch.randn(N, generator=g, device="cuda").to(tdt) if bias else None
+    h = ops.FFHandler("cuda:0")
+    m = ops.LinearMeta(h, K, N, dtype=tdt, max_tokens_per_batch=1024)
+    outs = []
+    for _ in range(3):
+        out = torch.full((M, N), float("nan"), dtype=tdt, device="cuda")
+        ops.Linear.inference_kernel_wrapper(m, None, x, out, w, b, K, N, M)
+        outs.append(out)
+    torch.cuda.synchronize()
+    want = x.float() @ w.float().T
+    if bias:
+        want = want + b.float()[None, :]
+    got = outs[0].float()
+    assert torch.isfinite(got).all()
+    tol = 2e-3 if dtype == "half" else 1.2e-2
+    assert (got - want).abs().max().item() <= tol * max(1.0, want.abs().max().item())
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
