@@ -290,7 +290,27 @@ int launch_tc4(void const *in, void *out, void const *w, void const *bias, int d
   FFB_SET_MAX_SMEM_ONCE(linear_tc4_kernel<T>, ((size_t)225 << 10) + 1024);
   size_t const smem = (size_t)stages * stage + 16384 + 1024; // ring + epilogue staging + alignment slack
   int const units = ((M + 255) / 256) * (((N + BN - 1) / BN) / 2);
-  dim3 grid(4 * std::min(units, kNumSMs / 4));
+  // how many 4-CTA clusters the device holds at once: GPCs whose SM count is not a multiple of 4 lose some (33 of 37 on
+  // a 148-SM B200); clusters beyond that would start only when the first ones exit
+  static int max_clusters[2] = {0, 0};
+  int &mc = max_clusters[dtype == FFB_DT_HALF ? 0 : 1];
+  if (mc == 0) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(kNumSMs / 4 * 4);
+    cfg.blockDim = dim3(T2_THREADS);
+    cfg.dynamicSmemBytes = ((size_t)209 << 10) + 16384 + 1024;
+    int nc = 0;
+    if (cudaOccupancyMaxActiveClusters(&nc, linear_tc4_kernel<T>, &cfg) != cudaSuccess || nc <= 0) {
+      (void)cudaGetLastError();
+      nc = kNumSMs / 4 - 5;
+    }
+    mc = std::min(nc, kNumSMs / 4);
+  }
+  dim3 grid(4 * std::min(units, mc));
+  if (ffb::env("FFB_TC4_DEBUG")) {
+    fprintf(stderr, "[ffb] linear_tc4: M=%d N=%d K=%d BN=%d stages=%d units=%d grid=%u max_active_clusters=%d\n", M, N, K, BN, stages,
+            units, grid.x, mc);
+  }
   linear_tc4_kernel<T><<<grid, T2_THREADS, smem, s>>>(tmA, tmB, (T *)out, (T const *)bias, M, N, K, BN, stages);
   FFB_LAUNCH_CHECK();
   return FFB_OK;
@@ -302,7 +322,7 @@ int launch_tc4(void const *in, void *out, void const *w, void const *bias, int d
 // clusters in whole waves (cost of a wave ~ max(tensor time ~ BN, fabric time ~ 128 + BN) per k-block; under-filled
 // waves are charged as in linear_tc2).  Returns 0 when no width qualifies (the caller keeps linear_tc2).
 int linear_tc4_pick_bn(int M, int N) {
-  int const clusters = kNumSMs / 4;
+  int const clusters = 33; // resident 4-CTA clusters on a 148-SM B200 (launch_tc4 measures it)
   long const mt = (M + 255) / 256;
   int bn = 0;
   double best = -1.0;

@@ -208,16 +208,22 @@ def test_linear_sk_stream_k(M, K, N, bias, dtype, monkeypatch):
 
 
 @pytest.mark.parametrize("dtype", ["half", "bf16"])
-@pytest.mark.parametrize("M,K,N,bias", [(512, 4096, 12288, False), (300, 1024, 1024, True), (1024, 1024, 2048, True),
-                                        (1024, 512, 20480, False), (129, 2048, 512, True)])
-def test_linear_w512_tiles(M, K, N, bias, dtype, monkeypatch):
-    """256 x 512 tiles per SM pair (linear_w512.cu, forced with FFB_W512=1): two UMMAs per k-step against one A tile,
-    single-buffered 512-column accumulator; ragged M, several tiles per pair (160 tiles on 74 pairs: the accumulator
-    hand-over between tiles), the programmatic-dependent-launch prologue on back-to-back calls."""
+@pytest.mark.parametrize("M,K,N,bias,bn", [(512, 4096, 12288, False, None), (300, 1024, 1024, True, None),
+                                           (1024, 1024, 2048, True, None), (1024, 512, 20480, False, 512),
+                                           (129, 2048, 512, True, None), (512, 1024, 11008, True, None),
+                                           (512, 512, 12288, False, 400), (260, 1024, 4128, True, 464)])
+def test_linear_w512_tiles(M, K, N, bias, bn, dtype, monkeypatch):
+    """One wave of wide tiles per SM pair (linear_w512.cu, forced with FFB_W512=1): 256 x BN tiles, 272 <= BN <= 512 chosen
+    so that all tiles fit the 74 pairs (336 for 512 x 12288, 304 for 512 x 11008), two UMMAs of unequal width per k-step
+    against one A tile, single-buffered accumulator; ragged M and ragged last column block (N = 4128), forced widths
+    with several tiles per pair (160 tiles of 512 on 74 pairs: the accumulator hand-over between tiles), the
+    programmatic-dependent-launch prologue on back-to-back calls."""
     import torch
     from flexflow_b200 import ops
     monkeypatch.setenv("FFB_LINEAR", "tc")
     monkeypatch.setenv("FFB_W512", "1")
+    if bn is not None:
+        monkeypatch.setenv("FFB_W512_BN", str(bn))
     ffb_lib.reload_env()
     tdt = torch.float16 if dtype == "half" else torch.bfloat16
     g = torch.Generator(device="cuda").manual_seed(43)
