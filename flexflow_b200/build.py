@@ -23,7 +23,7 @@ SOURCES = [
     "linear_qgemv.cu",
     "linear_tc.cu",
     "linear_tc2.cu",
-    "linear_tc4.cu", "linear_sk.cu", "linear_static.cu", "linear_qtc.cu", "linear_w512.cu",
+    "linear_tc4.cu", "linear_sk.cu", "linear_static.cu", "linear_qtc.cu", "linear_w512.cu", "linear_tcc.cu",
     "linear_tcq.cu",
     "capi_linear.cu",
     "comm.cu",

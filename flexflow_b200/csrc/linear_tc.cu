@@ -237,6 +237,8 @@ int linear_sk_supported(int dtype, int M, int K, int N, void const *ws, int cons
 int launch_linear_sk(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N,
                      void *ws, int *cnt, cudaStream_t s);
 // linear_w512.cu: 256 x 512 tiles per SM pair (two UMMAs per k-step against one A tile), one wave
+int linear_tcc_supported(int dtype, int M, int K, int N);
+int launch_linear_tcc(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N, cudaStream_t s);
 int linear_w512_supported(int dtype, int M, int K, int N);
 int launch_linear_w512(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N, cudaStream_t s);
 size_t linear_tc2_ws_bytes();
@@ -318,6 +320,10 @@ int launch_linear_tc(LinearTcState *st, int dtype, int quant, void const *in, vo
       return rc;
     }
     wd = st->scratch;
+  }
+  // up to 128 tokens: one 128-feature tile per cluster, the reduction dimension split over its CTAs (linear_tcc.cu)
+  if (M <= 128 && linear_tcc_supported(dtype, M, K, N)) {
+    return launch_linear_tcc(dtype, in, out, wd, bias, M, K, N, s);
   }
   // M > 128 (or an N the 128-wide 1-SM tiles do not divide): SM-pair tiles (linear_tc2.cu)
   if (M > 128 && linear_tc4_supported(dtype, M, K, N)) {

@@ -246,3 +246,55 @@ def test_linear_w512_tiles(M, K, N, bias, bn, dtype, monkeypatch):
     tol = 2e-3 if dtype == "half" else 1.2e-2
     assert (got - want).abs().max().item() <= tol * max(1.0, want.abs().max().item())
     assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+
+
+@pytest.mark.parametrize("dtype", ["half", "bf16"])
+@pytest.mark.parametrize("M,K,N,bias,split", [(64, 4096, 4096, False, None), (17, 1024, 12288, True, None),
+                                              (128, 2048, 4128, True, None), (100, 11008, 4096, False, None),
+                                              (33, 512, 256, True, None), (48, 4096, 32000, False, None),
+                                              (128, 1024, 1024, True, 8), (40, 4096, 2048, True, 2),
+                                              (96, 1024, 4096, False, 1)])
+def test_linear_tcc_cluster_split_k(M, K, N, bias, split, dtype, monkeypatch):
+    """17..128 tokens: one 128-feature tile per thread-block cluster, the reduction dimension split over its 2 / 4 / 8
+    CTAs and summed through distributed shared memory in rank order (linear_tcc.cu): o_proj (32 tiles x 4), K = 11008
+    (172 k-blocks over 4 CTAs: uneven ranges), tiny layers (2 tiles x 8), no split (qkv_proj, N = 32000), ragged N (4128),
+    token quarters without rows (M = 17, 33, 40); three calls on one handle give the same bits.  Against fp32 torch on the
+    rounded inputs and against linear_tc's one-CTA-per-tile result."""
+    import torch
+    from flexflow_b200 import ops
+    monkeypatch.setenv("FFB_LINEAR", "tc")
+    if split is not None:
+        monkeypatch.setenv("FFB_TCC_SPLIT", str(split))
+    ffb_lib.reload_env()
+    tdt = torch.float16 if dtype == "half" else torch.bfloat16
+    rng = np.random.default_rng(47)
+    x = O.round_to_dt(rng.standard_normal((M, K)).astype(np.float32), dtype)
+    w = O.round_to_dt((rng.standard_normal((N, K)) * 0.05).astype(np.float32), dtype)
+    b = O.round_to_dt(rng.standard_normal(N).astype(np.float32), dtype) if bias else None
+    h = ops.FFHandler("cuda:0")
+    m = ops.LinearMeta(h, K, N, dtype=tdt, max_tokens_per_batch=128)
+    xd, wd = torch.from_numpy(x).to("cuda", tdt), torch.from_numpy(w).to("cuda", tdt)
+    bd = torch.from_numpy(b).to("cuda", tdt) if bias else None
+    outs = []
+    for _ in range(3):
+        out = torch.full((M, N), float("nan"), dtype=tdt, device="cuda")
+        ops.Linear.inference_kernel_wrapper(m, None, xd, out, wd, bd, K, N, M)
+        outs.append(out)
+    torch.cuda.synchronize()
+    want = torch.from_numpy(x).cuda() @ torch.from_numpy(w).cuda().T  # fp32 on the rounded inputs
+    if bias:
+        want = want + torch.from_numpy(b).cuda()[None, :]
+    got = outs[0].float()
+    assert torch.isfinite(got).all()
+    tol = 2e-3 if dtype == "half" else 1.2e-2
+    assert (got - want).abs().max().item() <= tol * max(1.0, want.abs().max().item())
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+    # the one-CTA-per-tile kernel (no k split) on the same inputs: equal up to the rounding of differently ordered fp32 sums
+    monkeypatch.setenv("FFB_TCC", "0")
+    ffb_lib.reload_env()
+    ref = torch.full((M, N), float("nan"), dtype=tdt, device="cuda")
+    ops.Linear.inference_kernel_wrapper(m, None, xd, ref, wd, bd, K, N, M)
+    torch.cuda.synchronize()
+    assert (ref.float() - got).abs().max().item() <= tol * max(1.0, want.abs().max().item())
+    monkeypatch.delenv("FFB_TCC")
+    ffb_lib.reload_env()
