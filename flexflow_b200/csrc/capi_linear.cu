@@ -108,12 +108,12 @@ int ffb_linear_forward(ffb_linear_t h, void const *in, void *out, void const *w,
   // FFB_LINEAR=stream|tc forces a path (tests / profiling)
   char const *force = ffb::env("FFB_LINEAR");
   // Dense weights: up to 16 tokens the persistent bulk-copy GEMV, above that the tcgen05 kernels: at 17..128 tokens one
-  // 128-row tile per 128 output features streams the weights once (7B qkv_proj at 64 tokens: 23 us against 65 us in
-  // the mma.sync stream kernel) - provided there are enough feature tiles to pull from HBM with (o_proj, 32 tiles:
-  // only from 48 tokens).  Quantised weights: in-register dequantisation in the stream kernel up to 64 tokens,
+  // 128..256-feature tile per thread-block cluster streams the weights once, the reduction dimension split over the
+  // cluster's CTAs when the layer has few tiles (linear_tcc.cu; 7B o_proj at 32 tokens: 10.7 us against 13.4 us in the
+  // mma.sync stream kernel).  Quantised weights: in-register dequantisation in the stream kernel up to 64 tokens,
   // dequantise-then-GEMM above.  Env FFB_TC_MIN overrides.
   static int const tc_min_env = ffb::env("FFB_TC_MIN") ? atoi(ffb::env("FFB_TC_MIN")) : 0;
-  int const tc_min = tc_min_env > 0 ? tc_min_env : (d.quant_type != FFB_DT_NONE ? 65 : (d.out_dim >= 8192 ? 17 : 48));
+  int const tc_min = tc_min_env > 0 ? tc_min_env : (d.quant_type != FFB_DT_NONE ? 65 : 17);
   bool use_tc = h->tc && batch >= tc_min;
   if (force && strcmp(force, "stream") == 0) {
     use_tc = false;

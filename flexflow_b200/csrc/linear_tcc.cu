@@ -22,9 +22,9 @@ namespace ffb {
 using namespace tc;
 namespace {
 
-constexpr int CC_BM = 128, CC_BN = 128, CC_BK = 64, CC_THREADS = 256, CC_STAGES = 6;
-constexpr uint32_t CC_A_BYTES = CC_BM * CC_BK * 2, CC_B_BYTES = CC_BN * CC_BK * 2, CC_STAGE = CC_A_BYTES + CC_B_BYTES;
-constexpr size_t CC_SMEM = (size_t)CC_STAGES * CC_STAGE + 1024; // the 64 KB partial tile reuses the ring
+constexpr int CC_BM = 128, CC_BK = 64, CC_THREADS = 256, CC_MAX_STAGES = 6;
+constexpr uint32_t CC_A_BYTES = CC_BM * CC_BK * 2;
+constexpr size_t CC_RING_BYTES = (size_t)192 << 10, CC_SMEM = CC_RING_BYTES + 1024; // the partial tile (<= 128 KB) reuses the ring
 
 __device__ __forceinline__ uint32_t cc_ctarank() {
   uint32_t r;
@@ -56,9 +56,12 @@ __device__ __forceinline__ void cc_cluster_sync() {
 template <typename T>
 __global__ void __launch_bounds__(CC_THREADS, 1)
 linear_tcc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  T *__restrict__ out, T const *__restrict__ bias, int M, int N, int K, int a_rows) {
+                  T *__restrict__ out, T const *__restrict__ bias, int M, int N, int K, int a_rows, int CC_BN,
+                  int CC_STAGES) {
+  // CC_BN: tile width = UMMA N (128 by default; 192 / 256 by FFB_TCC_BN)
+  uint32_t const CC_B_BYTES = (uint32_t)CC_BN * CC_BK * 2, CC_STAGE = CC_A_BYTES + CC_B_BYTES;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t full_bar[CC_STAGES], empty_bar[CC_STAGES], tmem_full_bar;
+  __shared__ __align__(8) uint64_t full_bar[CC_MAX_STAGES], empty_bar[CC_MAX_STAGES], tmem_full_bar;
   __shared__ uint32_t tmem_base_smem;
   uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u); // 128B-swizzled tiles: 1024-byte alignment
 
@@ -81,8 +84,9 @@ linear_tcc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     mbar_init(&tmem_full_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 2) { // 128 fp32 accumulator columns
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "r"(128u));
+  uint32_t const tmem_cols = CC_BN > 128 ? 256u : 128u;
+  if (warp == 2) { // CC_BN fp32 accumulator columns
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "r"(tmem_cols));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
   }
   tc_fence_before();
@@ -114,7 +118,7 @@ linear_tcc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   } else if (warp == 1 && lane == 0) {
     // ===== MMA issuer =====
     constexpr uint32_t fmt = std::is_same<T, __nv_bfloat16>::value ? 1u : 0u;
-    constexpr uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(CC_BN >> 3) << 17) | ((uint32_t)(CC_BM >> 4) << 24);
+    uint32_t const idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(CC_BN >> 3) << 17) | ((uint32_t)(CC_BM >> 4) << 24);
     for (int n = 0; n < kb1 - kb0; n++) {
       int const s = n % CC_STAGES;
       mbar_wait(&full_bar[s], (n / CC_STAGES) & 1);
@@ -172,7 +176,7 @@ linear_tcc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // ===== step 2: every CTA of the cluster sums its S-th of the columns over all partials, in rank order =====
     cc_cluster_sync(); // all partials are in place (release / acquire at cluster scope)
     if (epi && has_rows) {
-      int const cw = CC_BN / S; // 64, 32 or 16 columns
+      int const cw = CC_BN / S; // a multiple of 16 (host)
       uint32_t const base = smem_u32(part) + (uint32_t)(rank * cw * CC_BM + row) * 4u;
       uint32_t src[8];
       for (int j = 0; j < S; j++) {
@@ -213,19 +217,20 @@ linear_tcc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   }
   if (warp == 2) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u));
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols));
   }
 }
 
 template <typename T>
-int launch_cc(void const *in, void *out, void const *w, void const *bias, int dtype, int M, int K, int N, int S, cudaStream_t s) {
+int launch_cc(void const *in, void *out, void const *w, void const *bias, int dtype, int M, int K, int N, int BN, int S,
+              cudaStream_t s) {
   int const a_rows = std::min(CC_BM, (M + 7) / 8 * 8);
   CUtensorMap tmA, tmB;
   int rc = make_tensor_map_2d(&tmA, dtype, in, M, K, a_rows);
   if (rc != FFB_OK) {
     return rc;
   }
-  rc = make_tensor_map_2d(&tmB, dtype, w, N, K, CC_BN);
+  rc = make_tensor_map_2d(&tmB, dtype, w, N, K, BN);
   if (rc != FFB_OK) {
     return rc;
   }
@@ -238,7 +243,8 @@ int launch_cc(void const *in, void *out, void const *w, void const *bias, int dt
       done = true;
     }
   }
-  int const n_tiles = (N + CC_BN - 1) / CC_BN;
+  int const n_tiles = (N + BN - 1) / BN;
+  int const stages = std::min<int>(CC_MAX_STAGES, (int)(CC_RING_BYTES / (CC_A_BYTES + (size_t)BN * CC_BK * 2)));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(n_tiles * S);
   cfg.blockDim = dim3(CC_THREADS);
@@ -253,28 +259,44 @@ int launch_cc(void const *in, void *out, void const *w, void const *bias, int dt
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = gemm_pdl_enabled() ? 2 : 1;
-  FFB_CUDA_TRY(cudaLaunchKernelEx(&cfg, linear_tcc_kernel<T>, tmA, tmB, (T *)out, (T const *)bias, M, N, K, a_rows));
+  FFB_CUDA_TRY(cudaLaunchKernelEx(&cfg, linear_tcc_kernel<T>, tmA, tmB, (T *)out, (T const *)bias, M, N, K, a_rows, BN, stages));
   return FFB_OK;
 }
 
 } // namespace
 
-// The k-split: the largest S in {8, 4, 2} with tiles x S <= SMs and at least 4 k-blocks per CTA; 1 otherwise (then the
-// kernel is linear_tc's schedule).  FFB_TCC_SPLIT overrides (1, 2, 4, 8 or 16).
-int linear_tcc_pick_split(int K, int N) {
-  int const n_tiles = (N + CC_BN - 1) / CC_BN, num_k = K / CC_BK;
+// Tile width and k-split.  Default: 128-feature tiles, S = the largest of {4, 2} with tiles x S <= SMs and >= 4 k-blocks
+// per CTA (7B o_proj: 32 tiles x 4), else 1.  Measured alternatives (FFB_TCC_BN = 128 / 192 / 256, FFB_TCC_SPLIT = 1 / 2 /
+// 4 / 8 / 16 force them; BN / S must be a multiple of 16): wider tiles with a deeper split do not help - qkv_proj at 64
+// tokens is 22.8 us with 64 tiles of 192 x 2 against 22.0 us with 96 tiles of 128 (the layer is at its HBM time plus
+// fixed costs either way), and clusters of 8 are far slower (o_proj, 16 tiles of 256 x 8: 23.9 against 11.7 us).
+void linear_tcc_pick(int M, int K, int N, int *bn_out, int *s_out) {
+  (void)M;
+  int const num_k = K / CC_BK;
+  int best_bn = 128, best_s = 1;
+  for (int S = 4; S >= 2; S /= 2) {
+    if (((N + 127) / 128) * S <= kNumSMs && num_k >= 4 * S) {
+      best_s = S;
+      break;
+    }
+  }
+  if (char const *e = env("FFB_TCC_BN")) {
+    int const v = atoi(e);
+    if (v == 128 || v == 192 || v == 256) {
+      best_bn = v;
+      if ((best_bn / best_s) % 16 != 0) {
+        best_s = 1;
+      }
+    }
+  }
   if (char const *e = env("FFB_TCC_SPLIT")) {
     int const v = atoi(e);
-    if ((v == 1 || v == 2 || v == 4 || v == 8 || v == 16) && num_k >= v) {
-      return v;
+    if ((v == 1 || v == 2 || v == 4 || v == 8 || v == 16) && num_k >= v && (best_bn / v) % 16 == 0) {
+      best_s = v;
     }
   }
-  for (int S = 8; S >= 2; S /= 2) {
-    if (n_tiles * S <= kNumSMs && num_k >= 4 * S) {
-      return S;
-    }
-  }
-  return 1;
+  *bn_out = best_bn;
+  *s_out = best_s;
 }
 
 // up to 128 tokens of dense weights.  FFB_TCC=0 disables it (linear_tc's one CTA per 128 features then).
@@ -288,11 +310,12 @@ int linear_tcc_supported(int dtype, int M, int K, int N) {
 }
 
 int launch_linear_tcc(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N, cudaStream_t s) {
-  int const S = linear_tcc_pick_split(K, N);
+  int bn = 128, S = 1;
+  linear_tcc_pick(M, K, N, &bn, &S);
   if (dtype == FFB_DT_HALF) {
-    return launch_cc<__half>(in, out, w, bias, dtype, M, K, N, S, s);
+    return launch_cc<__half>(in, out, w, bias, dtype, M, K, N, bn, S, s);
   }
-  return launch_cc<__nv_bfloat16>(in, out, w, bias, dtype, M, K, N, S, s);
+  return launch_cc<__nv_bfloat16>(in, out, w, bias, dtype, M, K, N, bn, S, s);
 }
 
 } // namespace ffb

@@ -249,21 +249,24 @@ def test_linear_w512_tiles(M, K, N, bias, bn, dtype, monkeypatch):
 
 
 @pytest.mark.parametrize("dtype", ["half", "bf16"])
-@pytest.mark.parametrize("M,K,N,bias,split", [(64, 4096, 4096, False, None), (17, 1024, 12288, True, None),
-                                              (128, 2048, 4128, True, None), (100, 11008, 4096, False, None),
-                                              (33, 512, 256, True, None), (48, 4096, 32000, False, None),
-                                              (128, 1024, 1024, True, 8), (40, 4096, 2048, True, 2),
-                                              (96, 1024, 4096, False, 1)])
-def test_linear_tcc_cluster_split_k(M, K, N, bias, split, dtype, monkeypatch):
-    """17..128 tokens: one 128-feature tile per thread-block cluster, the reduction dimension split over its 2 / 4 / 8
-    CTAs and summed through distributed shared memory in rank order (linear_tcc.cu): o_proj (32 tiles x 4), K = 11008
-    (172 k-blocks over 4 CTAs: uneven ranges), tiny layers (2 tiles x 8), no split (qkv_proj, N = 32000), ragged N (4128),
-    token quarters without rows (M = 17, 33, 40); three calls on one handle give the same bits.  Against fp32 torch on the
-    rounded inputs and against linear_tc's one-CTA-per-tile result."""
+@pytest.mark.parametrize("M,K,N,bias,bn,split", [(64, 4096, 4096, False, None, None), (17, 1024, 12288, True, None, None),
+                                                 (128, 2048, 4128, True, None, None), (100, 11008, 4096, False, None, None),
+                                                 (33, 512, 256, True, None, None), (48, 4096, 32000, False, None, None),
+                                                 (64, 4096, 12288, False, None, None), (128, 4096, 11008, True, None, None),
+                                                 (128, 1024, 1024, True, 128, 8), (40, 4096, 2048, True, 128, 2),
+                                                 (96, 1024, 4096, False, 128, 1), (72, 2048, 4128, True, 192, 4),
+                                                 (128, 1024, 2048, True, 256, 8), (24, 512, 1280, False, 256, 1)])
+def test_linear_tcc_cluster_split_k(M, K, N, bias, bn, split, dtype, monkeypatch):
+    """17..128 tokens: one tile of 128 / 192 / 256 features per thread-block cluster, the reduction dimension split over
+    its 2 / 4 / 8 CTAs and summed through distributed shared memory in rank order (linear_tcc.cu): o_proj (32 tiles x 4),
+    qkv_proj (64 tiles of 192 x 2), K = 11008 (172 k-blocks over 4 CTAs: uneven ranges), tiny layers (2 tiles x 8), no
+    split (N = 32000), ragged N (4128), token quarters without rows (M = 17, 24, 33, 40); three calls on one handle give
+    the same bits.  Against fp32 torch on the rounded inputs and against linear_tc's one-CTA-per-tile result."""
     import torch
     from flexflow_b200 import ops
     monkeypatch.setenv("FFB_LINEAR", "tc")
     if split is not None:
+        monkeypatch.setenv("FFB_TCC_BN", str(bn))
         monkeypatch.setenv("FFB_TCC_SPLIT", str(split))
     ffb_lib.reload_env()
     tdt = torch.float16 if dtype == "half" else torch.bfloat16
