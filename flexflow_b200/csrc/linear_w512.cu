@@ -238,7 +238,7 @@ linear_w512_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 
 template <typename T>
 int launch_w5(void const *in, void *out, void const *w, void const *bias, int dtype, int M, int K, int N, int BN, cudaStream_t s) {
-  int const H1 = (BN / 2 + 31) / 32 * 32, H2 = BN - H1; // both multiples of 16 (BN % 16 == 0), 128 <= H2 <= H1 <= 256
+  int const H1 = (BN / 2 + 31) / 32 * 32, H2 = BN - H1; // both multiples of 16 (BN % 16 == 0), 112 <= H2 <= H1 <= 256
   CUtensorMap tmA, tmB, tmB2;
   int rc = make_tensor_map_2d(&tmA, dtype, in, M, K, W5_BM);
   if (rc != FFB_OK) {
