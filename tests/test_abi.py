@@ -118,3 +118,13 @@ def test_cpp_host_mirror_compiles(tmp_path):
     src.write_text('#include "ffb_ops.h"\nint main() { return sizeof(ffb::FFHandler) > 0 ? 0 : 1; }\n')
     subprocess.run(["g++", "-std=c++17", "-fsyntax-only", "-I", os.path.join(ROOT, "include"),
                     "-I", os.path.join(ROOT, "flexflow_b200", "host"), str(src)], check=True)
+
+
+def test_every_kernel_source_is_in_the_build_list():
+    """A .cu file under csrc/ that is not in build.SOURCES would compile nowhere: __graft_entry__.build() and the GPU box
+    would run without it and the dispatcher's `extern` declaration would fail only at link time."""
+    import os
+    from flexflow_b200 import build
+    csrc = os.path.join(os.path.dirname(os.path.abspath(build.__file__)), "csrc")
+    on_disk = sorted(f for f in os.listdir(csrc) if f.endswith(".cu"))
+    assert sorted(build.SOURCES) == on_disk
