@@ -335,6 +335,10 @@ int launch_linear_tc(LinearTcState *st, int dtype, int quant, void const *in, vo
   if (linear_sk_supported(dtype, M, K, N, st->splitk_ws, st->splitk_cnt)) {
     return launch_linear_sk(dtype, in, out, wd, bias, M, K, N, st->splitk_ws, st->splitk_cnt, s);
   }
+  // more tokens on a narrow layer: the same cluster split per (128-token block, tile) where the pair kernel has few tiles
+  if (M > 128 && !ffb::env("FFB_TC2_BN") && !ffb::env("FFB_TC2_SPLIT") && linear_tcc_supported(dtype, M, K, N)) {
+    return launch_linear_tcc(dtype, in, out, wd, bias, M, K, N, s);
+  }
   if ((M > 128 || N % 128 != 0) && linear_tc2_supported(dtype, M, K, N)) {
     return launch_linear_tc2(dtype, in, out, wd, bias, M, K, N, st->splitk_ws, st->splitk_cnt, s);
   }

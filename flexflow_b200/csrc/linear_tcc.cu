@@ -67,7 +67,7 @@ linear_tcc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   int const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int const S = (int)cc_nctarank(), rank = (int)cc_ctarank();
-  int const tile = (int)blockIdx.x / S;
+  int const tile = (int)blockIdx.x / S, m0 = (int)blockIdx.y * CC_BM; // (clusters run along x: one tile, one 128-token block)
   int const num_k = K / CC_BK;
   int const kb0 = (int)((long)rank * num_k / S), kb1 = (int)((long)(rank + 1) * num_k / S); // (host: num_k >= S)
   uint32_t const stage_tx = (uint32_t)a_rows * CC_BK * 2 + CC_B_BYTES;
@@ -113,7 +113,7 @@ linear_tcc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         mbar_expect_tx(&full_bar[s], stage_tx);
         tma_load_2d(st + CC_A_BYTES, &tmB, (kb0 + n) * CC_BK, tile * CC_BN, &full_bar[s]);
       }
-      tma_load_2d(st, &tmA, (kb0 + n) * CC_BK, 0, &full_bar[s]);
+      tma_load_2d(st, &tmA, (kb0 + n) * CC_BK, m0, &full_bar[s]);
     }
   } else if (warp == 1 && lane == 0) {
     // ===== MMA issuer =====
@@ -135,8 +135,8 @@ linear_tcc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   }
   // ===== epilogue, step 1 (warps 4-7): the partial tile, TMEM -> this CTA's shared memory as [column][row] fp32 =====
   float *const part = reinterpret_cast<float *>(smem);
-  int const q = warp & 3, row = q * 32 + lane;
-  bool const epi = warp >= 4, has_rows = q * 32 < M; // (uniform across the cluster)
+  int const q = warp & 3, row = q * 32 + lane, row_g = m0 + row;
+  bool const epi = warp >= 4, has_rows = m0 + q * 32 < M; // (uniform across the cluster)
   int const col0 = tile * CC_BN;
   if (epi) {
     mbar_wait(&tmem_full_bar, 0); // every UMMA has completed: the ring is idle, the accumulator final
@@ -148,7 +148,7 @@ linear_tcc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         uint32_t r[32];
         tmem_ld32(tsrc + (uint32_t)c0, r);
         if (S == 1) { // no split: store
-          if (row < M) {
+          if (row_g < M) {
 #pragma unroll
             for (int v = 0; v < 4; v++) {
               int const col = col0 + c0 + v * 8;
@@ -158,7 +158,7 @@ linear_tcc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 for (int e = 0; e < 8; e++) {
                   f[e] = __uint_as_float(r[v * 8 + e]) + (bias ? DT<T>::to_f(bias[col + e]) : 0.f);
                 }
-                *reinterpret_cast<uint4 *>(out + (size_t)row * N + col) = pack8<T>(f);
+                *reinterpret_cast<uint4 *>(out + (size_t)row_g * N + col) = pack8<T>(f);
               }
             }
           }
@@ -176,14 +176,15 @@ linear_tcc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // ===== step 2: every CTA of the cluster sums its S-th of the columns over all partials, in rank order =====
     cc_cluster_sync(); // all partials are in place (release / acquire at cluster scope)
     if (epi && has_rows) {
-      int const cw = CC_BN / S; // a multiple of 16 (host)
-      uint32_t const base = smem_u32(part) + (uint32_t)(rank * cw * CC_BM + row) * 4u;
-      uint32_t src[8];
+      // columns [c_begin, c_end): CC_BN / S rounded up to 16 per rank (S = 3: 48 / 48 / 32 of 128), the last ranks take less
+      int const cw = (CC_BN / S + 15) / 16 * 16, c_begin = rank * cw, c_end = min(CC_BN, c_begin + cw);
+      uint32_t const base = smem_u32(part) + (uint32_t)row * 4u;
+      uint32_t src[8]; // (host: S <= 8)
       for (int j = 0; j < S; j++) {
         src[j] = cc_mapa(base, (uint32_t)j);
       }
 #pragma unroll 1
-      for (int c0 = 0; c0 < cw; c0 += 16) {
+      for (int c0 = c_begin; c0 < c_end; c0 += 16) {
         float acc[16];
 #pragma unroll
         for (int e = 0; e < 16; e++) {
@@ -195,17 +196,17 @@ linear_tcc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             acc[e] += cc_ld_dsmem(src[j] + (uint32_t)((c0 + e) * CC_BM) * 4u);
           }
         }
-        if (row < M) {
+        if (row_g < M) {
 #pragma unroll
           for (int v = 0; v < 2; v++) {
-            int const col = col0 + rank * cw + c0 + v * 8;
+            int const col = col0 + c0 + v * 8;
             if (col < N) {
               float f[8];
 #pragma unroll
               for (int e = 0; e < 8; e++) {
                 f[e] = acc[v * 8 + e] + (bias ? DT<T>::to_f(bias[col + e]) : 0.f);
               }
-              *reinterpret_cast<uint4 *>(out + (size_t)row * N + col) = pack8<T>(f);
+              *reinterpret_cast<uint4 *>(out + (size_t)row_g * N + col) = pack8<T>(f);
             }
           }
         }
@@ -224,7 +225,7 @@ linear_tcc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 template <typename T>
 int launch_cc(void const *in, void *out, void const *w, void const *bias, int dtype, int M, int K, int N, int BN, int S,
               cudaStream_t s) {
-  int const a_rows = std::min(CC_BM, (M + 7) / 8 * 8);
+  int const a_rows = std::min(CC_BM, (M + 7) / 8 * 8); // (more than 128 tokens: full boxes, the last block zero-filled)
   CUtensorMap tmA, tmB;
   int rc = make_tensor_map_2d(&tmA, dtype, in, M, K, a_rows);
   if (rc != FFB_OK) {
@@ -235,18 +236,10 @@ int launch_cc(void const *in, void *out, void const *w, void const *bias, int dt
     return rc;
   }
   FFB_SET_MAX_SMEM_ONCE(linear_tcc_kernel<T>, CC_SMEM);
-  if (S > 8) {
-    static bool np_set[2] = {false, false};
-    bool &done = np_set[dtype == FFB_DT_HALF ? 0 : 1];
-    if (!done) {
-      FFB_CUDA_TRY(cudaFuncSetAttribute(linear_tcc_kernel<T>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-      done = true;
-    }
-  }
   int const n_tiles = (N + BN - 1) / BN;
   int const stages = std::min<int>(CC_MAX_STAGES, (int)(CC_RING_BYTES / (CC_A_BYTES + (size_t)BN * CC_BK * 2)));
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(n_tiles * S);
+  cfg.gridDim = dim3(n_tiles * S, (M + CC_BM - 1) / CC_BM);
   cfg.blockDim = dim3(CC_THREADS);
   cfg.dynamicSmemBytes = CC_SMEM;
   cfg.stream = s;
@@ -265,33 +258,33 @@ int launch_cc(void const *in, void *out, void const *w, void const *bias, int dt
 
 } // namespace
 
-// Tile width and k-split.  Default: 128-feature tiles, S = the largest of {4, 2} with tiles x S <= SMs and >= 4 k-blocks
-// per CTA (7B o_proj: 32 tiles x 4), else 1.  Measured alternatives (FFB_TCC_BN = 128 / 192 / 256, FFB_TCC_SPLIT = 1 / 2 /
-// 4 / 8 / 16 force them; BN / S must be a multiple of 16): wider tiles with a deeper split do not help - qkv_proj at 64
-// tokens is 22.8 us with 64 tiles of 192 x 2 against 22.0 us with 96 tiles of 128 (the layer is at its HBM time plus
-// fixed costs either way), and clusters of 8 are far slower (o_proj, 16 tiles of 256 x 8: 23.9 against 11.7 us).
+// Tile width and k-split.  All clusters must be resident at once: a 148-SM B200 holds 33 clusters of 4 CTAs and 74 of 2
+// (GPCs whose SM count is not a multiple of the cluster size lose some), and a cluster beyond that starts when the
+// first ones exit (36 clusters of 4: 21.4 us where the SM-pair kernel takes 17.5).  Default: 128-feature tiles, S = 4
+// when (token blocks x tiles) <= 33, S = 2 when <= 74, each CTA keeping >= 4 k-blocks, else 1 (7B o_proj up to 128
+// tokens: 32 tiles x 4).  Measured alternatives (FFB_TCC_BN = 128 / 192 / 256, FFB_TCC_SPLIT = 1 .. 8 force them): wider
+// tiles with a deeper split do not help - qkv_proj at 64 tokens is 22.8 us with 64 tiles of 192 x 2 against 22.0 us with
+// 96 tiles of 128 (the layer is at its HBM time plus fixed costs either way); clusters of 8 are far slower (o_proj, 16
+// tiles of 256 x 8: 23.9 against 11.7 us); clusters of 3 (48 of them) 25.5 against 17.7 us.
+constexpr int kClusters4 = 33, kClusters2 = kNumSMs / 2;
+
 void linear_tcc_pick(int M, int K, int N, int *bn_out, int *s_out) {
-  (void)M;
-  int const num_k = K / CC_BK;
+  int const num_k = K / CC_BK, units = ((M + CC_BM - 1) / CC_BM) * ((N + 127) / 128);
   int best_bn = 128, best_s = 1;
-  for (int S = 4; S >= 2; S /= 2) {
-    if (((N + 127) / 128) * S <= kNumSMs && num_k >= 4 * S) {
-      best_s = S;
-      break;
-    }
+  if (units <= kClusters4 && num_k >= 16) {
+    best_s = 4;
+  } else if (units <= kClusters2 && num_k >= 8) {
+    best_s = 2;
   }
   if (char const *e = env("FFB_TCC_BN")) {
     int const v = atoi(e);
     if (v == 128 || v == 192 || v == 256) {
       best_bn = v;
-      if ((best_bn / best_s) % 16 != 0) {
-        best_s = 1;
-      }
     }
   }
   if (char const *e = env("FFB_TCC_SPLIT")) {
     int const v = atoi(e);
-    if ((v == 1 || v == 2 || v == 4 || v == 8 || v == 16) && num_k >= v && (best_bn / v) % 16 == 0) {
+    if (v >= 1 && v <= 8 && num_k >= v) {
       best_s = v;
     }
   }
@@ -299,14 +292,25 @@ void linear_tcc_pick(int M, int K, int N, int *bn_out, int *s_out) {
   *s_out = best_s;
 }
 
-// up to 128 tokens of dense weights.  FFB_TCC=0 disables it (linear_tc's one CTA per 128 features then).
+// Up to 128 tokens of dense weights: always.  Above that (up to 512 tokens, K >= 1024) only where the layer is so
+// narrow that the SM-pair kernel has a handful of tiles and at most its two-way split, and the clusters fill the chip:
+// (token blocks x 128-feature tiles) <= 33 (S = 4: 256 x 4096 x 2048 12.5 against 17.3 us, 512 x 4096 x 1024 12.2 against
+// 17.4 us) or 56 .. 74 (S = 2: o_proj at 256 tokens 16.1 against 18.5 us).
+// FFB_TCC=0 disables it (linear_tc's one CTA per 128 features / linear_tc2 then).
 int linear_tcc_supported(int dtype, int M, int K, int N) {
   if (char const *e = env("FFB_TCC")) {
     if (e[0] == '0') {
       return 0;
     }
   }
-  return (dtype == FFB_DT_HALF || dtype == FFB_DT_BF16) && M > 0 && M <= CC_BM && K % CC_BK == 0 && N % 8 == 0;
+  if (!((dtype == FFB_DT_HALF || dtype == FFB_DT_BF16) && M > 0 && K % CC_BK == 0 && N % 8 == 0)) {
+    return 0;
+  }
+  if (M <= CC_BM) {
+    return 1;
+  }
+  int const units = ((M + CC_BM - 1) / CC_BM) * ((N + 127) / 128);
+  return M <= 512 && K >= 1024 && (units <= kClusters4 || (units >= 56 && units <= kClusters2));
 }
 
 int launch_linear_tcc(int dtype, void const *in, void *out, void const *w, void const *bias, int M, int K, int N, cudaStream_t s) {

@@ -255,13 +255,17 @@ def test_linear_w512_tiles(M, K, N, bias, bn, dtype, monkeypatch):
                                                  (64, 4096, 12288, False, None, None), (128, 4096, 11008, True, None, None),
                                                  (128, 1024, 1024, True, 128, 8), (40, 4096, 2048, True, 128, 2),
                                                  (96, 1024, 4096, False, 128, 1), (72, 2048, 4128, True, 192, 4),
-                                                 (128, 1024, 2048, True, 256, 8), (24, 512, 1280, False, 256, 1)])
+                                                 (128, 1024, 2048, True, 256, 8), (24, 512, 1280, False, 256, 1),
+                                                 (512, 4096, 1536, False, 128, 3), (256, 4096, 4096, True, None, None),
+                                                 (300, 1024, 1024, True, None, None), (200, 2048, 256, False, None, None),
+                                                 (100, 1536, 1024, True, 128, 3), (384, 2048, 2080, True, 128, 3)])
 def test_linear_tcc_cluster_split_k(M, K, N, bias, bn, split, dtype, monkeypatch):
     """17..128 tokens: one tile of 128 / 192 / 256 features per thread-block cluster, the reduction dimension split over
     its 2 / 4 / 8 CTAs and summed through distributed shared memory in rank order (linear_tcc.cu): o_proj (32 tiles x 4),
     qkv_proj (64 tiles of 192 x 2), K = 11008 (172 k-blocks over 4 CTAs: uneven ranges), tiny layers (2 tiles x 8), no
-    split (N = 32000), ragged N (4128), token quarters without rows (M = 17, 24, 33, 40); three calls on one handle give
-    the same bits.  Against fp32 torch on the rounded inputs and against linear_tc's one-CTA-per-tile result."""
+    split (N = 32000), ragged N (4128), token quarters without rows (M = 17, 24, 33, 40); more than 128 tokens on narrow
+    layers (o_proj at 256 tokens: 2 token blocks x 32 tiles x 2; forced: 4 x 12 tiles x clusters of 3 with columns 48 / 48 / 32;
+    a ragged last token block, M = 300); three calls on one handle give the same bits.  Against fp32 torch on the rounded inputs and against linear_tc's one-CTA-per-tile result."""
     import torch
     from flexflow_b200 import ops
     monkeypatch.setenv("FFB_LINEAR", "tc")
@@ -275,7 +279,7 @@ def test_linear_tcc_cluster_split_k(M, K, N, bias, bn, split, dtype, monkeypatch
     w = O.round_to_dt((rng.standard_normal((N, K)) * 0.05).astype(np.float32), dtype)
     b = O.round_to_dt(rng.standard_normal(N).astype(np.float32), dtype) if bias else None
     h = ops.FFHandler("cuda:0")
-    m = ops.LinearMeta(h, K, N, dtype=tdt, max_tokens_per_batch=128)
+    m = ops.LinearMeta(h, K, N, dtype=tdt, max_tokens_per_batch=512)
     xd, wd = torch.from_numpy(x).to("cuda", tdt), torch.from_numpy(w).to("cuda", tdt)
     bd = torch.from_numpy(b).to("cuda", tdt) if bias else None
     outs = []
@@ -292,7 +296,7 @@ def test_linear_tcc_cluster_split_k(M, K, N, bias, bn, split, dtype, monkeypatch
     tol = 2e-3 if dtype == "half" else 1.2e-2
     assert (got - want).abs().max().item() <= tol * max(1.0, want.abs().max().item())
     assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
-    # the one-CTA-per-tile kernel (no k split) on the same inputs: equal up to the rounding of differently ordered fp32 sums
+    # the one-CTA-per-tile kernel (no k split; the SM-pair kernel above 128 tokens) on the same inputs: equal up to the rounding of differently ordered fp32 sums
     monkeypatch.setenv("FFB_TCC", "0")
     ffb_lib.reload_env()
     ref = torch.full((M, N), float("nan"), dtype=tdt, device="cuda")
